@@ -1,0 +1,206 @@
+/*
+ * espnet_b200_ctc.h -- C ABI of libespnet_b200_ctc.so
+ *
+ * The drop-in boundary for ESPnet's CTC hot path on B200 (sm_100a).
+ * Plain pointers, sizes and a cudaStream_t (passed as void*); no torch types,
+ * no C++ exceptions.  Every entry point returns 0 on success and a non-zero
+ * b200_status_t otherwise; b200_last_error() gives the thread-local message.
+ *
+ * All data pointers are DEVICE pointers unless the name ends in `_host`.
+ * All buffers are owned by the caller; the library never allocates device
+ * memory.  Calls are asynchronous and ordered on `stream`; they are safe to
+ * call concurrently from several host threads (torch.nn.DataParallel calls
+ * forward from one thread per GPU) because the library keeps no global
+ * mutable state beyond a per-device cache of kernel attributes and the
+ * thread-local error string.
+ *
+ * What each entry point replaces in the reference (kan-bayashi/espnet v0.9.5,
+ * paths relative to the reference root):
+ *
+ *   b200_ctc_loss_forward / _backward / _fwd_bwd
+ *       espnet2/asr/ctc.py:46-52  (CTC.loss_fn: log_softmax(2) + torch.nn.CTCLoss
+ *       (reduction=sum|none) + "/ th_pred.size(1)") and its autograd backward;
+ *       espnet/nets/pytorch_backend/ctc.py:52-65 (same, espnet1).
+ *   b200_ctc_prefix_init
+ *       espnet/nets/ctc_prefix_score.py:46-51 (in-place padding of x past xlens)
+ *       and :84-92 (initial r_prev = cumsum of blank log-probs).
+ *   b200_ctc_prefix_score
+ *       espnet/nets/ctc_prefix_score.py:69-188 (CTCPrefixScoreTH.__call__), the
+ *       score half: log_psi - s_prev for every (hypothesis, candidate).
+ *   b200_ctc_prefix_select
+ *       espnet/nets/ctc_prefix_score.py:190-221 (index_select_state) and
+ *       espnet/nets/scorers/ctc.py:41-64 (select_state): the forward variables
+ *       r (T,2) of the surviving (hypothesis, token) pairs only.
+ *   b200_ctc_greedy
+ *       espnet2/asr/ctc.py:103-111 (CTC.argmax over the vocabulary).
+ *   b200_ctc_viterbi
+ *       espnet/nets/pytorch_backend/ctc.py:153-216 (CTC.forced_align).
+ */
+#ifndef ESPNET_B200_CTC_H_
+#define ESPNET_B200_CTC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_CTC_ABI_VERSION 1
+
+typedef enum {
+  B200_OK = 0,
+  B200_ERR_INVALID_ARGUMENT = 1,
+  B200_ERR_MISALIGNED = 2,
+  B200_ERR_UNSUPPORTED_SHAPE = 3,
+  B200_ERR_WORKSPACE_TOO_SMALL = 4,
+  B200_ERR_CUDA = 5
+} b200_status_t;
+
+typedef enum {
+  B200_F32 = 0,
+  B200_BF16 = 1,
+  B200_F16 = 2
+} b200_dtype_t;
+
+/* The value CTCPrefixScoreTH uses for log(0) (ctc_prefix_score.py:34). */
+#define B200_CTC_LOGZERO (-10000000000.0f)
+
+/* ABI version of the loaded library (== B200_CTC_ABI_VERSION it was built with). */
+int b200_ctc_abi_version(void);
+
+/* Thread-local message of the last failing call on this thread ("" if none). */
+const char* b200_last_error(void);
+
+/* ------------------------------------------------------------------------
+ * CTC loss, fused log_softmax + alpha/beta lattice + gradient w.r.t. logits
+ * ------------------------------------------------------------------------
+ * logits      (T,B,V) view with element strides (stride_t, stride_b, 1); the
+ *             (B,T,V)-contiguous buffer ESPnet's ctc_lo produces, handed over
+ *             as its .transpose(0,1) view (espnet2/asr/ctc.py:82), is
+ *             stride_t = V, stride_b = T*V.
+ * targets     int64 label ids; utterance b's labels are
+ *             targets[tgt_offsets[b] .. tgt_offsets[b]+olen[b]).
+ * ilen, olen  int64 (B,) frame and label counts.
+ * Lmax        host-side upper bound on olen (sizes the lattice workspace).
+ * nll         fp32 (B,) out: -log p(y_b | x_b) in nats; +inf if no alignment
+ *             exists (torch.nn.CTCLoss, zero_infinity=False).
+ * workspace   b200_ctc_loss_workspace_bytes(...) bytes, 256-byte aligned; it
+ *             carries the lattice from _forward to _backward and must stay
+ *             untouched in between.
+ */
+size_t b200_ctc_loss_workspace_bytes(int64_t T, int64_t B, int64_t V, int64_t Lmax);
+
+int b200_ctc_loss_forward(const void* logits, int dtype,
+                          int64_t T, int64_t B, int64_t V,
+                          int64_t stride_t, int64_t stride_b,
+                          const int64_t* targets, const int64_t* tgt_offsets,
+                          const int64_t* ilen, const int64_t* olen,
+                          int64_t Lmax, int blank,
+                          float* nll, float* loss_sum /* may be NULL: sum_b nll[b] */,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* grad_logits[t,b,v] = grad_scale * grad_weight[b] *
+ *      (softmax(logits[t,b,:])[v] - occupancy[t,b,v])        for t <  ilen[b]
+ *                    = 0                                     for t >= ilen[b]
+ * grad_weight may be NULL (== 1 for every utterance).  Utterances whose nll is
+ * +inf get NaN gradients for t < ilen[b], as torch does.
+ * grad_logits has the dtype of logits and element strides (gstride_t, gstride_b, 1).
+ * The logits, targets and lengths must be the ones given to _forward. */
+int b200_ctc_loss_backward(const void* logits, int dtype,
+                           int64_t T, int64_t B, int64_t V,
+                           int64_t stride_t, int64_t stride_b,
+                           const int64_t* targets, const int64_t* tgt_offsets,
+                           const int64_t* ilen, const int64_t* olen,
+                           int64_t Lmax, int blank,
+                           const float* grad_weight, float grad_scale,
+                           void* grad_logits, int64_t gstride_t, int64_t gstride_b,
+                           void* workspace, size_t workspace_bytes, void* stream);
+
+/* _forward followed by _backward in one call (training with a known upstream
+ * gradient, and the benchmark's "fwd+bwd" unit of work). */
+int b200_ctc_loss_fwd_bwd(const void* logits, int dtype,
+                          int64_t T, int64_t B, int64_t V,
+                          int64_t stride_t, int64_t stride_b,
+                          const int64_t* targets, const int64_t* tgt_offsets,
+                          const int64_t* ilen, const int64_t* olen,
+                          int64_t Lmax, int blank,
+                          const float* grad_weight, float grad_scale,
+                          float* nll, float* loss_sum,
+                          void* grad_logits, int64_t gstride_t, int64_t gstride_b,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------
+ * CTC prefix scoring (CTCPrefixScoreTH)
+ * ------------------------------------------------------------------------
+ * x        fp32 (B,T,V) contiguous log-probabilities (CTC.log_softmax output).
+ * xlens    int64 (B,).
+ * n_hyps   hypotheses per utterance; hypothesis h belongs to utterance h / n_hyps.
+ * r        fp32 (T,2,n_bh) forward variables: [:,0,:] non-blank, [:,1,:] blank.
+ */
+
+/* Pads x past xlens in place (x[b,t>=xlens[b],:] = logzero, blank column = 0),
+ * fills r0 (T,2,B): r0[:,0,:] = logzero, r0[:,1,b] = cumsum_t x[b,t,blank],
+ * and xmax (B,V): max_t x[b,t,v] (the per-token scale of b200_ctc_prefix_score). */
+int b200_ctc_prefix_init(float* x, const int64_t* xlens,
+                         int64_t B, int64_t T, int64_t V, int blank,
+                         float* r0, float* xmax, void* stream);
+
+/* One step of prefix scoring.
+ * r_prev      (T,2,n_bh)   state of the n_bh prefixes
+ * s_prev      (n_bh,) or NULL (== 0): log_psi of each prefix
+ * last_ids    int64 (n_bh,) last label of each prefix
+ * output_len  len(prefix) - 1 (without <sos>), identical for all prefixes
+ * scoring_ids int64 (n_bh,snum) candidates per prefix, or NULL (snum = 0): all V
+ * start, end  frame window (ctc_prefix_score.py:145-154)
+ * scores      fp32 (n_bh,V) out: log_psi - s_prev; logzero - s_prev for tokens
+ *             not in scoring_ids and for blank; eos gets r_sum[xlens-1].
+ * log_psi     fp32 (n_bh,V) out (may alias nothing; needed by _select)
+ * work        fp32 scratch of b200_ctc_prefix_work_floats(T, n_bh) floats */
+size_t b200_ctc_prefix_work_floats(int64_t T, int64_t n_bh);
+
+int b200_ctc_prefix_score(const float* x, const float* xmax, const int64_t* xlens,
+                          int64_t B, int64_t T, int64_t V, int64_t n_hyps,
+                          int blank, int eos,
+                          const float* r_prev, const float* s_prev,
+                          const int64_t* last_ids, int64_t output_len,
+                          const int64_t* scoring_ids, int64_t snum,
+                          int64_t start, int64_t end,
+                          float* scores, float* log_psi, float* work, void* stream);
+
+/* Forward variables of the survivors: for new hypothesis k (0..n_new) with
+ * parent hypothesis parent[k] (index into the n_bh prefixes of the step that
+ * produced `work`) and appended token token[k]:
+ *   r_new[t,:,k] for t in [0,T)   and   s_new[k] = log_psi[parent[k], token[k]].
+ * Uses the phi rows that b200_ctc_prefix_score left in `work`. */
+int b200_ctc_prefix_select(const float* x, int64_t B, int64_t T, int64_t V,
+                           int64_t n_hyps, int blank,
+                           const float* r_prev, const float* log_psi,
+                           const int64_t* last_ids, int64_t output_len,
+                           int64_t start, int64_t end, int64_t n_bh,
+                           const int64_t* parent, const int64_t* token, int64_t n_new,
+                           const float* work,
+                           float* r_new, float* s_new, void* stream);
+
+/* ------------------------------------------------------------------------
+ * Greedy path and forced alignment
+ * ------------------------------------------------------------------------ */
+
+/* ids[b,t] = argmax_v logits[b,t,v] (first maximum), int64, for a (B,T,V) view
+ * with element strides (stride_b, stride_t, 1). */
+int b200_ctc_greedy(const void* logits, int dtype, int64_t B, int64_t T, int64_t V,
+                    int64_t stride_b, int64_t stride_t, int64_t* ids, void* stream);
+
+/* Viterbi alignment of one utterance: lpz fp32 (T,V) log-probs, y int64 (L,),
+ * align int64 (T,) out: the label (or blank) emitted at each frame.
+ * work: (T * (2L+1)) int16 back-pointers + 2*(2L+1) doubles, see
+ * b200_ctc_viterbi_work_bytes. */
+size_t b200_ctc_viterbi_work_bytes(int64_t T, int64_t L);
+int b200_ctc_viterbi(const float* lpz, int64_t T, int64_t V,
+                     const int64_t* y, int64_t L, int blank,
+                     int64_t* align, void* work, size_t work_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ESPNET_B200_CTC_H_ */
