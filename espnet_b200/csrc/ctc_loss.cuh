@@ -1,0 +1,79 @@
+// ctc_loss.cuh -- parameter block and workspace layout shared by the CTC loss kernels.
+//
+// Replaces espnet2/asr/ctc.py:46-52 (CTC.loss_fn: log_softmax + torch.nn.CTCLoss + /B)
+// and its autograd backward.  Three kernels, all in log2 units:
+//
+//   rowstats  (stream)  one warp per (utterance, frame) row: the row is staged in shared
+//                       memory by a 1-D bulk (TMA) copy, reduced to its log-sum-exp, and the
+//                       blank + label columns are gathered into lpg[b][t][0..L].
+//   sweep     (latency) one CTA per (utterance, direction): the alpha (or, on the reversed
+//                       sequence, beta) recursion over lpg, one thread per label position,
+//                       re-centred every frame so that values stay O(10) in fp32.
+//   grad      (stream)  one warp per row again: occupancies from alpha+beta, normalised per
+//                       row, softmax recomputed from the staged row, result written in place
+//                       in shared memory and bulk-stored to the gradient.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+struct LossWs {
+  float* lse2;      // [B][T]      row log2-sum-exp (log2 units)
+  float* lpg;       // [B][T][Kp]  log2-prob of blank (k=0) and label k-1 (k>=1)
+  float* lat;       // [2][B][T][Sp] alpha (dir 0) and beta in reversed-state order (dir 1)
+  int* labels;      // [B][Kp]     labels as int32
+  int* dup_next;    // [B][Kp]     next position with the same label, or -1
+  int* is_first;    // [B][Kp]     1 if no earlier position has the same label
+  float* logz_beta; // [B]         log2 p(y|x) from the beta sweep (consistency check)
+  float* nll_ws;    // [B]         copy of nll (nats) kept for the backward pass
+  int* bad;         // [1]         set when a label is outside [0,V) or equals blank
+  int64_t Kp, Sp;
+  size_t bytes;
+};
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Carves the workspace; base may be NULL to only compute the size.
+inline LossWs carve_loss_ws(void* base, int64_t T, int64_t B, int64_t V, int64_t Lmax) {
+  (void)V;
+  LossWs w;
+  w.Kp = (int64_t)align_up((size_t)(Lmax + 1), 8);
+  w.Sp = 2 * w.Kp;
+  size_t off = 0;
+  char* p = (char*)base;
+  auto take = [&](size_t n) { size_t o = off; off = align_up(off + n, 256); return p ? p + o : (char*)0; };
+  w.lse2 = (float*)take(sizeof(float) * B * T);
+  w.lpg = (float*)take(sizeof(float) * B * T * w.Kp);
+  w.lat = (float*)take(sizeof(float) * 2 * B * T * w.Sp);
+  w.labels = (int*)take(sizeof(int) * B * w.Kp);
+  w.dup_next = (int*)take(sizeof(int) * B * w.Kp);
+  w.is_first = (int*)take(sizeof(int) * B * w.Kp);
+  w.logz_beta = (float*)take(sizeof(float) * B);
+  w.nll_ws = (float*)take(sizeof(float) * B);
+  w.bad = (int*)take(sizeof(int) * 64);
+  w.bytes = off;
+  return w;
+}
+
+struct LossParams {
+  const void* logits;
+  void* grad;
+  int64_t T, B, V;
+  int64_t stride_t, stride_b;    // logits element strides
+  int64_t gstride_t, gstride_b;  // gradient element strides
+  const int64_t* targets;
+  const int64_t* tgt_offsets;
+  const int64_t* ilen;
+  const int64_t* olen;
+  int64_t Lmax;
+  int blank;
+  const float* grad_weight;
+  float grad_scale;
+  float* nll;
+  LossWs ws;
+  int b0, b1;     // utterance range handled by this launch
+  int row_bytes;  // shared-memory bytes per staged row (multiple of 16)
+  int stages;
+};
+
+}  // namespace b200

@@ -1,0 +1,219 @@
+// ctc_loss_host.inl -- argument checks, launch configuration and the extern "C" entry
+// points of the CTC loss (included by ctc_loss.cu).
+namespace b200 {
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+static int elem_size(int dtype) { return dtype == B200_F32 ? 4 : 2; }
+
+struct RowsCfg {
+  int warps, stages, row_bytes, smem_bytes, grid;
+  bool bulk;
+};
+
+// Shared-memory budget of the streaming kernels: leave room on the SM for a
+// resident sweep CTA (they overlap with the streams of other utterance groups).
+static const int kRowsSmemBudget = 200 * 1024;
+
+static int plan_rows(const LossParams& p, int dtype, bool grad_kernel, bool bulk, RowsCfg* c) {
+  const int es = elem_size(dtype);
+  c->bulk = bulk;
+  c->row_bytes = (int)align_up((size_t)p.V * es, 16);
+  const int scratch = grad_kernel ? (int)((p.ws.Sp + p.ws.Kp) * sizeof(float)) : 0;
+  int budget = max_smem_optin();
+  if (budget > kRowsSmemBudget) budget = kRowsSmemBudget;
+  int best_w = 0, best_s = 0;
+  for (int stages = 3; stages >= 2 && best_w == 0; --stages) {
+    const int per_warp = stages * c->row_bytes + scratch;
+    for (int w = 8; w >= 1; --w) {
+      const int bar = (w * stages * 8 + 127) & ~127;
+      if (bar + w * per_warp <= budget) { best_w = w; best_s = stages; break; }
+    }
+    // prefer 3 stages only if at least 4 warps fit
+    if (stages == 3 && best_w > 0 && best_w < 4) { best_w = 0; }
+  }
+  if (best_w == 0) {
+    set_error("vocabulary too large for the staged-row kernels: V=%lld needs %d bytes per row",
+              (long long)p.V, c->row_bytes);
+    return B200_ERR_UNSUPPORTED_SHAPE;
+  }
+  c->warps = best_w;
+  c->stages = best_s;
+  c->smem_bytes = ((best_w * best_s * 8 + 127) & ~127) + best_w * (best_s * c->row_bytes + scratch);
+  const int64_t rows = (int64_t)(p.b1 - p.b0) * p.T;
+  int64_t g = (rows + best_w - 1) / best_w;
+  const int sms = num_sms();
+  if (g > sms) g = sms;
+  if (g < 1) g = 1;
+  c->grid = (int)g;
+  return B200_OK;
+}
+
+template <typename T, bool BULK, bool GRAD>
+static int launch_rows_t(LossParams p, const RowsCfg& c, cudaStream_t st) {
+  auto kern = ctc_rows_kernel<T, BULK, GRAD>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes));
+  p.row_bytes = c.row_bytes;
+  p.stages = c.stages;
+  kern<<<c.grid, c.warps * 32, c.smem_bytes, st>>>(p);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+template <bool GRAD>
+static int launch_rows(const LossParams& p, int dtype, const RowsCfg& c, cudaStream_t st) {
+  switch (dtype) {
+    case B200_F32:
+      return c.bulk ? launch_rows_t<float, true, GRAD>(p, c, st) : launch_rows_t<float, false, GRAD>(p, c, st);
+    case B200_BF16:
+      return c.bulk ? launch_rows_t<__nv_bfloat16, true, GRAD>(p, c, st)
+                    : launch_rows_t<__nv_bfloat16, false, GRAD>(p, c, st);
+    case B200_F16:
+      return c.bulk ? launch_rows_t<__half, true, GRAD>(p, c, st) : launch_rows_t<__half, false, GRAD>(p, c, st);
+  }
+  set_error("unknown dtype %d", dtype);
+  return B200_ERR_INVALID_ARGUMENT;
+}
+
+static int check_common(const void* logits, int dtype, int64_t T, int64_t B, int64_t V, int64_t stride_t,
+                        int64_t stride_b, const int64_t* targets, const int64_t* tgt_offsets,
+                        const int64_t* ilen, const int64_t* olen, int64_t Lmax, int blank, void* workspace,
+                        size_t workspace_bytes) {
+  B200_CHECK_ARG(dtype == B200_F32 || dtype == B200_BF16 || dtype == B200_F16, B200_ERR_INVALID_ARGUMENT,
+                 "dtype must be B200_F32, B200_BF16 or B200_F16, got %d", dtype);
+  B200_CHECK_ARG(T >= 1 && B >= 1 && V >= 2, B200_ERR_INVALID_ARGUMENT,
+                 "need T>=1, B>=1, V>=2, got T=%lld B=%lld V=%lld", (long long)T, (long long)B, (long long)V);
+  B200_CHECK_ARG(T < (1ll << 30) && B < (1ll << 30) && V < (1ll << 30), B200_ERR_INVALID_ARGUMENT,
+                 "T, B, V must each be below 2^30");
+  B200_CHECK_ARG(logits && ilen && olen && tgt_offsets && (targets || Lmax == 0), B200_ERR_INVALID_ARGUMENT,
+                 "null pointer argument");
+  B200_CHECK_ARG(stride_t >= 0 && stride_b >= 0, B200_ERR_INVALID_ARGUMENT, "negative logits stride");
+  B200_CHECK_ARG(blank >= 0 && blank < V, B200_ERR_INVALID_ARGUMENT, "blank=%d outside [0,%lld)", blank,
+                 (long long)V);
+  B200_CHECK_ARG(Lmax >= 0, B200_ERR_INVALID_ARGUMENT, "Lmax=%lld is negative", (long long)Lmax);
+  B200_CHECK_ARG(Lmax + 1 <= 1024, B200_ERR_UNSUPPORTED_SHAPE,
+                 "Lmax=%lld: the lattice sweep supports at most 1023 labels per utterance", (long long)Lmax);
+  B200_CHECK_ARG(workspace != nullptr, B200_ERR_INVALID_ARGUMENT, "workspace is null");
+  B200_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, B200_ERR_MISALIGNED,
+                 "workspace must be 256-byte aligned");
+  const size_t need = carve_loss_ws(nullptr, T, B, V, Lmax).bytes;
+  B200_CHECK_ARG(workspace_bytes >= need, B200_ERR_WORKSPACE_TOO_SMALL, "workspace has %zu bytes, need %zu",
+                 workspace_bytes, need);
+  return B200_OK;
+}
+
+static bool rows_bulk_ok(const void* base, int64_t V, int64_t st, int64_t sb, int es) {
+  return aligned16(base) && (V * es) % 16 == 0 && (st * es) % 16 == 0 && (sb * es) % 16 == 0;
+}
+
+static LossParams make_params(const void* logits, int64_t T, int64_t B, int64_t V, int64_t stride_t,
+                              int64_t stride_b, const int64_t* targets, const int64_t* tgt_offsets,
+                              const int64_t* ilen, const int64_t* olen, int64_t Lmax, int blank, float* nll,
+                              void* workspace) {
+  LossParams p;
+  memset(&p, 0, sizeof(p));
+  p.logits = logits;
+  p.T = T; p.B = B; p.V = V;
+  p.stride_t = stride_t; p.stride_b = stride_b;
+  p.targets = targets; p.tgt_offsets = tgt_offsets;
+  p.ilen = ilen; p.olen = olen;
+  p.Lmax = Lmax; p.blank = blank;
+  p.nll = nll;
+  p.ws = carve_loss_ws(workspace, T, B, V, Lmax);
+  p.b0 = 0; p.b1 = (int)B;
+  return p;
+}
+
+static int run_forward(LossParams p, int dtype, float* loss_sum, cudaStream_t st) {
+  const int es = elem_size(dtype);
+  RowsCfg cfg;
+  int rc = plan_rows(p, dtype, false, rows_bulk_ok(p.logits, p.V, p.stride_t, p.stride_b, es), &cfg);
+  if (rc) return rc;
+  B200_CUDA(cudaMemsetAsync(p.ws.bad, 0, sizeof(int), st));
+  {
+    int threads = (int)align_up((size_t)(p.Lmax > 0 ? p.Lmax : 1), 32);
+    if (threads > 1024) threads = 1024;
+    const size_t sm = sizeof(int) * (size_t)(p.Lmax > 0 ? p.Lmax : 1);
+    ctc_prep_kernel<<<(unsigned)(p.b1 - p.b0), threads, sm, st>>>(p);
+    B200_CUDA(cudaGetLastError());
+  }
+  rc = launch_rows<false>(p, dtype, cfg, st);
+  if (rc) return rc;
+  {
+    const int threads = (int)align_up((size_t)(p.Lmax + 1), 32);
+    dim3 grid((unsigned)(p.b1 - p.b0), 2);
+    ctc_sweep_kernel<<<grid, threads, 0, st>>>(p);
+    B200_CUDA(cudaGetLastError());
+  }
+  if (loss_sum) {
+    ctc_loss_sum_kernel<<<1, 32, 0, st>>>(p.nll, (int)p.B, loss_sum);
+    B200_CUDA(cudaGetLastError());
+  }
+  return B200_OK;
+}
+
+static int run_backward(LossParams p, int dtype, cudaStream_t st) {
+  const int es = elem_size(dtype);
+  const bool bulk = rows_bulk_ok(p.logits, p.V, p.stride_t, p.stride_b, es) &&
+                    rows_bulk_ok(p.grad, p.V, p.gstride_t, p.gstride_b, es);
+  RowsCfg cfg;
+  int rc = plan_rows(p, dtype, true, bulk, &cfg);
+  if (rc) return rc;
+  return launch_rows<true>(p, dtype, cfg, st);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" size_t b200_ctc_loss_workspace_bytes(int64_t T, int64_t B, int64_t V, int64_t Lmax) {
+  if (T < 1 || B < 1 || V < 1 || Lmax < 0) return 0;
+  return carve_loss_ws(nullptr, T, B, V, Lmax).bytes;
+}
+
+extern "C" int b200_ctc_loss_forward(const void* logits, int dtype, int64_t T, int64_t B, int64_t V,
+                                     int64_t stride_t, int64_t stride_b, const int64_t* targets,
+                                     const int64_t* tgt_offsets, const int64_t* ilen, const int64_t* olen,
+                                     int64_t Lmax, int blank, float* nll, float* loss_sum, void* workspace,
+                                     size_t workspace_bytes, void* stream) {
+  int rc = check_common(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
+                        blank, workspace, workspace_bytes);
+  if (rc) return rc;
+  B200_CHECK_ARG(nll != nullptr, B200_ERR_INVALID_ARGUMENT, "nll is null");
+  LossParams p = make_params(logits, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
+                             blank, nll, workspace);
+  return run_forward(p, dtype, loss_sum, (cudaStream_t)stream);
+}
+
+extern "C" int b200_ctc_loss_backward(const void* logits, int dtype, int64_t T, int64_t B, int64_t V,
+                                      int64_t stride_t, int64_t stride_b, const int64_t* targets,
+                                      const int64_t* tgt_offsets, const int64_t* ilen, const int64_t* olen,
+                                      int64_t Lmax, int blank, const float* grad_weight, float grad_scale,
+                                      void* grad_logits, int64_t gstride_t, int64_t gstride_b,
+                                      void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_common(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
+                        blank, workspace, workspace_bytes);
+  if (rc) return rc;
+  B200_CHECK_ARG(grad_logits != nullptr, B200_ERR_INVALID_ARGUMENT, "grad_logits is null");
+  B200_CHECK_ARG(gstride_t >= V || T == 1, B200_ERR_INVALID_ARGUMENT, "gradient rows overlap (gstride_t < V)");
+  LossParams p = make_params(logits, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
+                             blank, nullptr, workspace);
+  p.grad = grad_logits;
+  p.gstride_t = gstride_t; p.gstride_b = gstride_b;
+  p.grad_weight = grad_weight; p.grad_scale = grad_scale;
+  return run_backward(p, dtype, (cudaStream_t)stream);
+}
+
+extern "C" int b200_ctc_loss_fwd_bwd(const void* logits, int dtype, int64_t T, int64_t B, int64_t V,
+                                     int64_t stride_t, int64_t stride_b, const int64_t* targets,
+                                     const int64_t* tgt_offsets, const int64_t* ilen, const int64_t* olen,
+                                     int64_t Lmax, int blank, const float* grad_weight, float grad_scale,
+                                     float* nll, float* loss_sum, void* grad_logits, int64_t gstride_t,
+                                     int64_t gstride_b, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = b200_ctc_loss_forward(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen,
+                                 Lmax, blank, nll, loss_sum, workspace, workspace_bytes, stream);
+  if (rc) return rc;
+  return b200_ctc_loss_backward(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen,
+                                Lmax, blank, grad_weight, grad_scale, grad_logits, gstride_t, gstride_b,
+                                workspace, workspace_bytes, stream);
+}
