@@ -44,12 +44,21 @@ __global__ void ctc_prep_kernel(LossParams p) {
 // Thread i owns the logical states 2i (blank) and 2i+1 (label i).  dir 1 runs
 // the same recursion on the time- and label-reversed utterance, which is the
 // beta recursion; its states are stored in that reversed (logical) order.
-// Every frame the values are re-centred by floor(max of the previous frame) so
-// that they stay O(10): in fp32 that keeps ~1e-6 absolute resolution in log2
-// units however long the utterance is.  The integer offsets are summed exactly.
-constexpr int kSweepU = 4;  // frames of lpg prefetched per batch
+//
+// The label-gathered log-prob rows lpg[b][t][0..L] are staged into shared memory
+// kSweepRing chunks ahead by 1-D bulk copies (cp.async.bulk -> UBLKCP) that signal
+// an mbarrier, so the sequential loop never waits on global memory.
+//
+// Every frame the values are re-centred by an integer offset derived from the
+// maximum over all states three frames earlier (so that the reduction is off the
+// critical path).  Values therefore stay O(10..50) in log2 units and keep ~4e-6
+// absolute resolution in fp32 however long the utterance is; the integer offsets
+// are summed exactly.
+constexpr int kSweepRing = 4;
+constexpr int kSweepMaxChf = 8;  // frames per staged chunk (upper bound)
 
-__global__ void __launch_bounds__(1024) ctc_sweep_kernel(LossParams p) {
+__global__ void __launch_bounds__(1024) ctc_sweep_kernel(LossParams p, int chf) {
+  extern __shared__ __align__(128) unsigned char sw_smem[];
   const int b = p.b0 + blockIdx.x;
   const int dir = blockIdx.y;
   const int Tb = (int)p.ilen[b];
@@ -62,6 +71,9 @@ __global__ void __launch_bounds__(1024) ctc_sweep_kernel(LossParams p) {
   __shared__ float s_bnd[2][32];
   __shared__ float s_wmax[2][32];
   __shared__ float s_fin[2];
+  uint64_t* full = reinterpret_cast<uint64_t*>(sw_smem);
+  float* ring = reinterpret_cast<float*>(sw_smem + 128);
+  const int chunk_floats = chf * (int)Kp;
 
   if (Tb <= 0) {
     if (i == 0) {
@@ -71,7 +83,25 @@ __global__ void __launch_bounds__(1024) ctc_sweep_kernel(LossParams p) {
     return;
   }
   for (int k = i; k < 64; k += blockDim.x) { (&s_bnd[0][0])[k] = B200_NEG; (&s_wmax[0][0])[k] = B200_NEG; }
+  if (i == 0) {
+    for (int s = 0; s < kSweepRing; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
   __syncthreads();
+
+  const float* lpg = p.ws.lpg + (int64_t)b * p.T * Kp;
+  const int nchunks = (Tb + chf - 1) / chf;
+  auto issue_chunk = [&](int c) {  // thread 0 only
+    const int f0 = c * chf;
+    const int n = min(chf, Tb - f0);
+    const int phys0 = dir ? (Tb - f0 - n) : f0;
+    const int slot = c % kSweepRing;
+    const uint32_t bytes = (uint32_t)(n * Kp * sizeof(float));
+    mbar_arrive_expect_tx(&full[slot], bytes);
+    bulk_g2s(ring + (size_t)slot * chunk_floats, lpg + (int64_t)phys0 * Kp, bytes, &full[slot]);
+  };
+  if (i == 0)
+    for (int c = 0; c < kSweepRing - 1 && c < nchunks; ++c) issue_chunk(c);
 
   const int* lab = p.ws.labels + (int64_t)b * Kp;
   const bool has_label = i < L;
@@ -83,76 +113,69 @@ __global__ void __launch_bounds__(1024) ctc_sweep_kernel(LossParams p) {
     if (i >= 1) prev_lab = lab[dir ? pi + 1 : pi - 1];
   }
   const bool skip_ok = has_label && i >= 1 && my_lab != prev_lab;
-
-  const float* lpg = p.ws.lpg + (int64_t)b * p.T * Kp;
   float* out = p.ws.lat + (((int64_t)dir * p.B + b) * p.T) * Sp + 2 * i;
   const int kcol = has_label ? 1 + pi : 0;
 
-  float cb[kSweepU], cl[kSweepU], qb[kSweepU], ql[kSweepU];
-  auto load_batch = [&](int base, float* vb, float* vl) {
+  float ab = B200_NEG, al = B200_NEG;
+  int c_m2 = 0, c_m1 = 0, c_cur = 0;  // cumulative offsets of frames tt-2, tt-1, tt
+
+  for (int c = 0; c < nchunks; ++c) {
+    const int slot = c % kSweepRing;
+    const int f0 = c * chf;
+    const int n = min(chf, Tb - f0);
+    // fill the slot freed by the previous chunk (its last frame ended with a barrier)
+    if (i == 0 && c + kSweepRing - 1 < nchunks) issue_chunk(c + kSweepRing - 1);
+    mbar_wait(&full[slot], (uint32_t)((c / kSweepRing) & 1));
+    const float* buf = ring + (size_t)slot * chunk_floats;
+    float vb[kSweepMaxChf], vl[kSweepMaxChf];
 #pragma unroll
-    for (int j = 0; j < kSweepU; ++j) {
-      const int tt = base + j;
-      if (tt < Tb) {
-        const int t = dir ? (Tb - 1 - tt) : tt;
-        const float* row = lpg + (int64_t)t * Kp;
-        vb[j] = __ldg(row);
-        vl[j] = __ldg(row + kcol);
+    for (int f = 0; f < kSweepMaxChf; ++f) {
+      if (f < n) {
+        const float* rowp = buf + (size_t)(dir ? (n - 1 - f) : f) * Kp;
+        vb[f] = rowp[0];
+        vl[f] = rowp[kcol];
       } else {
-        vb[j] = 0.f; vl[j] = 0.f;
+        vb[f] = 0.f; vl[f] = 0.f;
       }
     }
-  };
-
-  // frame 0
-  float ab = B200_NEG, al = B200_NEG;
-  {
-    const int t0 = dir ? (Tb - 1) : 0;
-    const float* row = lpg + (int64_t)t0 * Kp;
-    if (i == 0) {
-      ab = __ldg(row);
-      if (has_label) al = __ldg(row + kcol);
-    }
-    if (active) *reinterpret_cast<float2*>(out + (int64_t)t0 * Sp) = make_float2(ab, al);
-    float m = warp_max_redux(fmaxf(ab, al));
-    if (lane == 31) s_bnd[0][warp] = al;
-    if (lane == 0) s_wmax[0][warp] = m;
-  }
-  int csum = 0;
-  load_batch(1, cb, cl);
-  __syncthreads();
-
-  for (int base = 1; base < Tb; base += kSweepU) {
-    load_batch(base + kSweepU, qb, ql);
 #pragma unroll
-    for (int j = 0; j < kSweepU; ++j) {
-      const int tt = base + j;
-      if (tt < Tb) {
-        const int rd = (tt - 1) & 1, wr = tt & 1;
-        // neighbour: label state of the previous logical position
-        float nb = __shfl_up_sync(0xffffffffu, al, 1);
-        if (lane == 0) nb = warp ? s_bnd[rd][warp - 1] : B200_NEG;
-        // re-centring offset: floor(max over all states of the previous frame)
-        const float pm = warp_max_redux(s_wmax[rd][lane]);
-        const float off = floorf(pm);
-        csum += (int)off;
-        const float lb = cb[j] - off;
-        const float ll = cl[j] - off;
-        const float nab = lb + lse2(ab, nb);
-        const float nal = ll + lse3(al, ab, skip_ok ? nb : B200_NEG);
-        ab = active ? nab : B200_NEG;
-        al = has_label ? nal : B200_NEG;
+    for (int f = 0; f < kSweepMaxChf; ++f) {
+      if (f < n) {
+        const int tt = f0 + f;
         const int t = dir ? (Tb - 1 - tt) : tt;
-        if (active) *reinterpret_cast<float2*>(out + (int64_t)t * Sp) = make_float2(ab, al);
-        const float m = warp_max_redux(fmaxf(ab, al));
-        if (lane == 31) s_bnd[wr][warp] = al;
-        if (lane == 0) s_wmax[wr][warp] = m;
+        if (tt == 0) {
+          if (i == 0) {
+            ab = vb[0];
+            if (has_label) al = vl[0];
+          }
+          if (active) *reinterpret_cast<float2*>(out + (int64_t)t * Sp) = make_float2(ab, al);
+          if (lane == 31) s_bnd[0][warp] = al;
+        } else {
+          const int rd = (tt - 1) & 1, wr = tt & 1;
+          // (a) off the critical path: offsets.  Publish the max of frame tt-1, pick up
+          //     the max of frame tt-2 and derive the cumulative offset of frame tt+1.
+          const float wm_prev = warp_max_redux(fmaxf(ab, al));
+          if (lane == 0) s_wmax[wr][warp] = wm_prev;
+          const float m2 = warp_max_redux(s_wmax[rd][lane]);
+          const int c_next = (m2 > -1.0e29f) ? (int)floorf(m2) + c_m2 : c_cur;
+          const float off = (float)(c_cur - c_m1);
+          // (b) the recursion
+          float nb = __shfl_up_sync(0xffffffffu, al, 1);
+          if (lane == 0) nb = warp ? s_bnd[rd][warp - 1] : B200_NEG;
+          const float nab = (vb[f] - off) + lse2(ab, nb);
+          const float nal = (vl[f] - off) + lse3(al, ab, skip_ok ? nb : B200_NEG);
+          ab = active ? nab : B200_NEG;
+          al = has_label ? nal : B200_NEG;
+          if (lane == 31) s_bnd[wr][warp] = al;
+          if (active) *reinterpret_cast<float2*>(out + (int64_t)t * Sp) = make_float2(ab, al);
+          c_m2 = c_m1; c_m1 = c_cur; c_cur = c_next;
+        }
         if (nw > 1) __syncthreads(); else __syncwarp();
       }
     }
-#pragma unroll
-    for (int j = 0; j < kSweepU; ++j) { cb[j] = qb[j]; cl[j] = ql[j]; }
   }
+  // after the loop c_m1 is the cumulative offset of the last frame (c_cur that of the next)
+  const int csum = (Tb > 1) ? c_m1 : 0;
 
   // log2 p(y|x) = lse2(state 2L, state 2L-1) + sum of offsets
   if (i == L) s_fin[0] = ab;

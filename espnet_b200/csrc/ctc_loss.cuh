@@ -26,7 +26,8 @@ struct LossWs {
   int* is_first;    // [B][Kp]     1 if no earlier position has the same label
   float* logz_beta; // [B]         log2 p(y|x) from the beta sweep (consistency check)
   float* nll_ws;    // [B]         copy of nll (nats) kept for the backward pass
-  int* bad;         // [1]         set when a label is outside [0,V) or equals blank
+  int* bad;         // [64]        [0] set when a label is outside [0,V) or equals blank;
+                    //             [1], [2] task counters of the rowstats / gradient kernels
   int64_t Kp, Sp;
   size_t bytes;
 };
@@ -72,8 +73,6 @@ struct LossParams {
   float* nll;
   LossWs ws;
   int b0, b1;     // utterance range handled by this launch
-  int row_bytes;  // shared-memory bytes per staged row (multiple of 16)
-  int stages;
 };
 
 }  // namespace b200

@@ -7,41 +7,20 @@ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t
 static int elem_size(int dtype) { return dtype == B200_F32 ? 4 : 2; }
 
 struct RowsCfg {
-  int warps, stages, row_bytes, smem_bytes, grid;
-  bool bulk;
+  int smem_bytes, grid;
+  bool vec;
 };
 
-// Shared-memory budget of the streaming kernels: leave room on the SM for a
-// resident sweep CTA (they overlap with the streams of other utterance groups).
-static const int kRowsSmemBudget = 200 * 1024;
-
-static int plan_rows(const LossParams& p, int dtype, bool grad_kernel, bool bulk, RowsCfg* c) {
-  const int es = elem_size(dtype);
-  c->bulk = bulk;
-  c->row_bytes = (int)align_up((size_t)p.V * es, 16);
-  const int scratch = grad_kernel ? (int)((p.ws.Sp + p.ws.Kp) * sizeof(float)) : 0;
-  int budget = max_smem_optin();
-  if (budget > kRowsSmemBudget) budget = kRowsSmemBudget;
-  int best_w = 0, best_s = 0;
-  for (int stages = 3; stages >= 2 && best_w == 0; --stages) {
-    const int per_warp = stages * c->row_bytes + scratch;
-    for (int w = 8; w >= 1; --w) {
-      const int bar = (w * stages * 8 + 127) & ~127;
-      if (bar + w * per_warp <= budget) { best_w = w; best_s = stages; break; }
-    }
-    // prefer 3 stages only if at least 4 warps fit
-    if (stages == 3 && best_w > 0 && best_w < 4) { best_w = 0; }
-  }
-  if (best_w == 0) {
-    set_error("vocabulary too large for the staged-row kernels: V=%lld needs %d bytes per row",
-              (long long)p.V, c->row_bytes);
+static int plan_rows(const LossParams& p, bool grad_kernel, bool vec, RowsCfg* c) {
+  c->vec = vec;
+  c->smem_bytes = (int)(3 * p.ws.Kp * sizeof(int) + (grad_kernel ? kRowsWarps * p.ws.Sp * sizeof(float) : 0));
+  if (c->smem_bytes > max_smem_optin() - 1024) {
+    set_error("Lmax=%lld needs %d bytes of shared memory in the gradient kernel", (long long)p.Lmax,
+              c->smem_bytes);
     return B200_ERR_UNSUPPORTED_SHAPE;
   }
-  c->warps = best_w;
-  c->stages = best_s;
-  c->smem_bytes = ((best_w * best_s * 8 + 127) & ~127) + best_w * (best_s * c->row_bytes + scratch);
-  const int64_t rows = (int64_t)(p.b1 - p.b0) * p.T;
-  int64_t g = (rows + best_w - 1) / best_w;
+  const int nblk = (int)((p.T + kFramesPerTask - 1) / kFramesPerTask);
+  int64_t g = (int64_t)(p.b1 - p.b0) * nblk;
   const int sms = num_sms();
   if (g > sms) g = sms;
   if (g < 1) g = 1;
@@ -49,13 +28,12 @@ static int plan_rows(const LossParams& p, int dtype, bool grad_kernel, bool bulk
   return B200_OK;
 }
 
-template <typename T, bool BULK, bool GRAD>
-static int launch_rows_t(LossParams p, const RowsCfg& c, cudaStream_t st) {
-  auto kern = ctc_rows_kernel<T, BULK, GRAD>;
-  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes));
-  p.row_bytes = c.row_bytes;
-  p.stages = c.stages;
-  kern<<<c.grid, c.warps * 32, c.smem_bytes, st>>>(p);
+template <typename T, bool VEC, bool GRAD>
+static int launch_rows_t(const LossParams& p, const RowsCfg& c, cudaStream_t st) {
+  auto kern = ctc_rows_kernel<T, VEC, GRAD>;
+  if (c.smem_bytes > 48 * 1024)
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes));
+  kern<<<c.grid, kRowsWarps * 32, c.smem_bytes, st>>>(p);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }
@@ -64,12 +42,12 @@ template <bool GRAD>
 static int launch_rows(const LossParams& p, int dtype, const RowsCfg& c, cudaStream_t st) {
   switch (dtype) {
     case B200_F32:
-      return c.bulk ? launch_rows_t<float, true, GRAD>(p, c, st) : launch_rows_t<float, false, GRAD>(p, c, st);
+      return c.vec ? launch_rows_t<float, true, GRAD>(p, c, st) : launch_rows_t<float, false, GRAD>(p, c, st);
     case B200_BF16:
-      return c.bulk ? launch_rows_t<__nv_bfloat16, true, GRAD>(p, c, st)
-                    : launch_rows_t<__nv_bfloat16, false, GRAD>(p, c, st);
+      return c.vec ? launch_rows_t<__nv_bfloat16, true, GRAD>(p, c, st)
+                   : launch_rows_t<__nv_bfloat16, false, GRAD>(p, c, st);
     case B200_F16:
-      return c.bulk ? launch_rows_t<__half, true, GRAD>(p, c, st) : launch_rows_t<__half, false, GRAD>(p, c, st);
+      return c.vec ? launch_rows_t<__half, true, GRAD>(p, c, st) : launch_rows_t<__half, false, GRAD>(p, c, st);
   }
   set_error("unknown dtype %d", dtype);
   return B200_ERR_INVALID_ARGUMENT;
@@ -102,7 +80,7 @@ static int check_common(const void* logits, int dtype, int64_t T, int64_t B, int
   return B200_OK;
 }
 
-static bool rows_bulk_ok(const void* base, int64_t V, int64_t st, int64_t sb, int es) {
+static bool rows_vec_ok(const void* base, int64_t V, int64_t st, int64_t sb, int es) {
   return aligned16(base) && (V * es) % 16 == 0 && (st * es) % 16 == 0 && (sb * es) % 16 == 0;
 }
 
@@ -127,9 +105,9 @@ static LossParams make_params(const void* logits, int64_t T, int64_t B, int64_t 
 static int run_forward(LossParams p, int dtype, float* loss_sum, cudaStream_t st) {
   const int es = elem_size(dtype);
   RowsCfg cfg;
-  int rc = plan_rows(p, dtype, false, rows_bulk_ok(p.logits, p.V, p.stride_t, p.stride_b, es), &cfg);
+  int rc = plan_rows(p, false, rows_vec_ok(p.logits, p.V, p.stride_t, p.stride_b, es), &cfg);
   if (rc) return rc;
-  B200_CUDA(cudaMemsetAsync(p.ws.bad, 0, sizeof(int), st));
+  B200_CUDA(cudaMemsetAsync(p.ws.bad, 0, 64 * sizeof(int), st));
   {
     int threads = (int)align_up((size_t)(p.Lmax > 0 ? p.Lmax : 1), 32);
     if (threads > 1024) threads = 1024;
@@ -141,8 +119,14 @@ static int run_forward(LossParams p, int dtype, float* loss_sum, cudaStream_t st
   if (rc) return rc;
   {
     const int threads = (int)align_up((size_t)(p.Lmax + 1), 32);
+    int chf = (int)(16384 / (p.ws.Kp * sizeof(float)));
+    if (chf > kSweepMaxChf) chf = kSweepMaxChf;
+    if (chf < 1) chf = 1;
+    const int smem = 128 + kSweepRing * chf * (int)p.ws.Kp * (int)sizeof(float);
+    if (smem > 48 * 1024)
+      B200_CUDA(cudaFuncSetAttribute(ctc_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     dim3 grid((unsigned)(p.b1 - p.b0), 2);
-    ctc_sweep_kernel<<<grid, threads, 0, st>>>(p);
+    ctc_sweep_kernel<<<grid, threads, smem, st>>>(p, chf);
     B200_CUDA(cudaGetLastError());
   }
   if (loss_sum) {
@@ -154,11 +138,12 @@ static int run_forward(LossParams p, int dtype, float* loss_sum, cudaStream_t st
 
 static int run_backward(LossParams p, int dtype, cudaStream_t st) {
   const int es = elem_size(dtype);
-  const bool bulk = rows_bulk_ok(p.logits, p.V, p.stride_t, p.stride_b, es) &&
-                    rows_bulk_ok(p.grad, p.V, p.gstride_t, p.gstride_b, es);
+  const bool vec = rows_vec_ok(p.logits, p.V, p.stride_t, p.stride_b, es) &&
+                   rows_vec_ok(p.grad, p.V, p.gstride_t, p.gstride_b, es);
   RowsCfg cfg;
-  int rc = plan_rows(p, dtype, true, bulk, &cfg);
+  int rc = plan_rows(p, true, vec, &cfg);
   if (rc) return rc;
+  B200_CUDA(cudaMemsetAsync(p.ws.bad + 2, 0, sizeof(int), st));
   return launch_rows<true>(p, dtype, cfg, st);
 }
 
