@@ -7,6 +7,8 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include "../../include/espnet_b200_ctc.h"
 
@@ -224,6 +226,35 @@ __device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                : "l"(p));
   return r;
+}
+// raw (unconverted) element loads: issue several, convert later, so that the loads overlap
+__device__ __forceinline__ uint32_t ld_nc_raw(const float* p) {
+  uint32_t r;
+  asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint32_t ld_nc_raw(const __nv_bfloat16* p) {
+  unsigned short r;
+  asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint32_t ld_nc_raw(const __half* p) {
+  unsigned short r;
+  asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float ld_nc_f32(const float* p) {
+  float r;
+  asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(r) : "l"(p));
+  return r;
+}
+template <typename T> __device__ __forceinline__ float raw_to_float(uint32_t r);
+template <> __device__ __forceinline__ float raw_to_float<float>(uint32_t r) { return __uint_as_float(r); }
+template <> __device__ __forceinline__ float raw_to_float<__nv_bfloat16>(uint32_t r) {
+  return __uint_as_float(r << 16);
+}
+template <> __device__ __forceinline__ float raw_to_float<__half>(uint32_t r) {
+  return __half2float(__ushort_as_half((unsigned short)r));
 }
 __device__ __forceinline__ void st_cs_v4(void* p, const uint4& v) {
   asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),

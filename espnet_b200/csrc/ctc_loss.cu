@@ -49,11 +49,11 @@ __global__ void ctc_prep_kernel(LossParams p) {
 // kSweepRing chunks ahead by 1-D bulk copies (cp.async.bulk -> UBLKCP) that signal
 // an mbarrier, so the sequential loop never waits on global memory.
 //
-// Every frame the values are re-centred by an integer offset derived from the
-// maximum over all states three frames earlier (so that the reduction is off the
-// critical path).  Values therefore stay O(10..50) in log2 units and keep ~4e-6
-// absolute resolution in fp32 however long the utterance is; the integer offsets
-// are summed exactly.
+// Every frame the values are re-centred by an integer offset (a per-frame drift estimate
+// plus, once per staged chunk, the measured maximum over all states), so the reduction is
+// off the critical path.  Values therefore stay O(10..50) in log2 units and keep ~4e-6
+// absolute resolution in fp32 however long the utterance is; the integer offsets are
+// summed exactly.
 constexpr int kSweepRing = 4;
 constexpr int kSweepMaxChf = 8;  // frames per staged chunk (upper bound)
 
@@ -117,7 +117,14 @@ __global__ void __launch_bounds__(1024) ctc_sweep_kernel(LossParams p, int chf) 
   const int kcol = has_label ? 1 + pi : 0;
 
   float ab = B200_NEG, al = B200_NEG;
-  int c_m2 = 0, c_m1 = 0, c_cur = 0;  // cumulative offsets of frames tt-2, tt-1, tt
+  // Re-centring: every frame subtracts the integer `dstep`; once per chunk the level
+  // (max over all states) is measured and removed by a one-shot `corr`, and dstep is
+  // re-estimated from the measured drift.  csum is the exact sum of what was subtracted.
+  int csum = 0;
+  float dstep = 0.f, level_prev = 0.f, corr_prev = 0.f;
+  float* outp = out + (int64_t)(dir ? (Tb - 1) : 0) * Sp;
+  const int64_t ostep = dir ? -Sp : Sp;
+  const int bsrc = warp ? warp - 1 : 0;
 
   for (int c = 0; c < nchunks; ++c) {
     const int slot = c % kSweepRing;
@@ -133,49 +140,54 @@ __global__ void __launch_bounds__(1024) ctc_sweep_kernel(LossParams p, int chf) 
       if (f < n) {
         const float* rowp = buf + (size_t)(dir ? (n - 1 - f) : f) * Kp;
         vb[f] = rowp[0];
-        vl[f] = rowp[kcol];
+        vl[f] = has_label ? rowp[kcol] : B200_NEG;  // a missing label state stays at log(0)
       } else {
         vb[f] = 0.f; vl[f] = 0.f;
       }
     }
+    if (c == 0) {
+      // frame 0: only the first blank and the first label are reachable
+      if (i == 0) { ab = vb[0]; al = vl[0]; }
+      if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
+      outp += ostep;
+      if (lane == 31) s_bnd[0][warp] = al;
+      if (n > 1) dstep = floorf(vb[1]);
+    } else {
+      // publish this warp's level; it is picked up after the next barrier
+      const float wm = warp_max_redux(fmaxf(ab, al));
+      if (lane == 0) s_wmax[c & 1][warp] = wm;
+    }
+    if (nw > 1) __syncthreads(); else __syncwarp();
+    float corr = 0.f;
+    if (c > 0) {
+      const float level = warp_max_redux(s_wmax[c & 1][lane]);
+      corr = floorf(level);
+      // drift per frame seen over the last chunk, relative to the dstep that was applied
+      dstep = floorf(dstep + (level - level_prev + corr_prev) / (float)chf + 0.5f);
+      level_prev = level;
+      corr_prev = corr;
+    }
 #pragma unroll
     for (int f = 0; f < kSweepMaxChf; ++f) {
-      if (f < n) {
+      if (f < n && !(c == 0 && f == 0)) {
         const int tt = f0 + f;
-        const int t = dir ? (Tb - 1 - tt) : tt;
-        if (tt == 0) {
-          if (i == 0) {
-            ab = vb[0];
-            if (has_label) al = vl[0];
-          }
-          if (active) *reinterpret_cast<float2*>(out + (int64_t)t * Sp) = make_float2(ab, al);
-          if (lane == 31) s_bnd[0][warp] = al;
-        } else {
-          const int rd = (tt - 1) & 1, wr = tt & 1;
-          // (a) off the critical path: offsets.  Publish the max of frame tt-1, pick up
-          //     the max of frame tt-2 and derive the cumulative offset of frame tt+1.
-          const float wm_prev = warp_max_redux(fmaxf(ab, al));
-          if (lane == 0) s_wmax[wr][warp] = wm_prev;
-          const float m2 = warp_max_redux(s_wmax[rd][lane]);
-          const int c_next = (m2 > -1.0e29f) ? (int)floorf(m2) + c_m2 : c_cur;
-          const float off = (float)(c_cur - c_m1);
-          // (b) the recursion
-          float nb = __shfl_up_sync(0xffffffffu, al, 1);
-          if (lane == 0) nb = warp ? s_bnd[rd][warp - 1] : B200_NEG;
-          const float nab = (vb[f] - off) + lse2(ab, nb);
-          const float nal = (vl[f] - off) + lse3(al, ab, skip_ok ? nb : B200_NEG);
-          ab = active ? nab : B200_NEG;
-          al = has_label ? nal : B200_NEG;
-          if (lane == 31) s_bnd[wr][warp] = al;
-          if (active) *reinterpret_cast<float2*>(out + (int64_t)t * Sp) = make_float2(ab, al);
-          c_m2 = c_m1; c_m1 = c_cur; c_cur = c_next;
-        }
+        const int rd = (tt - 1) & 1, wr = tt & 1;
+        const float o = dstep + ((f == 0 || (c == 0 && f == 1)) ? corr : 0.f);
+        float nb = __shfl_up_sync(0xffffffffu, al, 1);
+        const float bn = s_bnd[rd][bsrc];
+        if (lane == 0) nb = warp ? bn : B200_NEG;
+        const float x = lse2(ab, nb);
+        const float y = lse3(al, ab, skip_ok ? nb : B200_NEG);
+        ab = (vb[f] - o) + x;
+        al = (vl[f] - o) + y;
+        csum += (int)o;
+        if (lane == 31) s_bnd[wr][warp] = al;
+        if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
+        outp += ostep;
         if (nw > 1) __syncthreads(); else __syncwarp();
       }
     }
   }
-  // after the loop c_m1 is the cumulative offset of the last frame (c_cur that of the next)
-  const int csum = (Tb > 1) ? c_m1 : 0;
 
   // log2 p(y|x) = lse2(state 2L, state 2L-1) + sum of offsets
   if (i == L) s_fin[0] = ab;
@@ -202,4 +214,5 @@ __global__ void ctc_loss_sum_kernel(const float* nll, int B, float* out) {
 }  // namespace b200
 
 #include "ctc_loss_rows.inl"
+#include "ctc_loss_gamma.inl"
 #include "ctc_loss_host.inl"

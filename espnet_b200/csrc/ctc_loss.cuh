@@ -21,13 +21,15 @@ struct LossWs {
   float* lse2;      // [B][T]      row log2-sum-exp (log2 units)
   float* lpg;       // [B][T][Kp]  log2-prob of blank (k=0) and label k-1 (k>=1)
   float* lat;       // [2][B][T][Sp] alpha (dir 0) and beta in reversed-state order (dir 1)
+  float* occ;       // [B][T][Kp]  occupancy of blank (k=0) / label k-1, duplicates merged into the
+                    //             first occurrence; -1 marks a later duplicate (nothing to write)
   int* labels;      // [B][Kp]     labels as int32
   int* dup_next;    // [B][Kp]     next position with the same label, or -1
   int* is_first;    // [B][Kp]     1 if no earlier position has the same label
   float* logz_beta; // [B]         log2 p(y|x) from the beta sweep (consistency check)
   float* nll_ws;    // [B]         copy of nll (nats) kept for the backward pass
   int* bad;         // [64]        [0] set when a label is outside [0,V) or equals blank;
-                    //             [1], [2] task counters of the rowstats / gradient kernels
+                    //             [1], [2], [3] task counters of the rowstats / gradient / occupancy kernels
   int64_t Kp, Sp;
   size_t bytes;
 };
@@ -46,6 +48,7 @@ inline LossWs carve_loss_ws(void* base, int64_t T, int64_t B, int64_t V, int64_t
   w.lse2 = (float*)take(sizeof(float) * B * T);
   w.lpg = (float*)take(sizeof(float) * B * T * w.Kp);
   w.lat = (float*)take(sizeof(float) * 2 * B * T * w.Sp);
+  w.occ = (float*)take(sizeof(float) * B * T * w.Kp);
   w.labels = (int*)take(sizeof(int) * B * w.Kp);
   w.dup_next = (int*)take(sizeof(int) * B * w.Kp);
   w.is_first = (int*)take(sizeof(int) * B * w.Kp);
@@ -73,6 +76,7 @@ struct LossParams {
   float* nll;
   LossWs ws;
   int b0, b1;     // utterance range handled by this launch
+  int debug;      // developer experiments (B200_DEBUG_VARIANT), 0 in production
 };
 
 }  // namespace b200

@@ -7,20 +7,28 @@ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t
 static int elem_size(int dtype) { return dtype == B200_F32 ? 4 : 2; }
 
 struct RowsCfg {
-  int smem_bytes, grid;
+  int smem_bytes, grid, warps;
   bool vec;
 };
 
+// Shared memory of the streaming kernels is capped so that a lattice-sweep CTA of another
+// utterance group can be resident on the same SM.
+static const int kRowsSmemBudget = 160 * 1024;
+
 static int plan_rows(const LossParams& p, bool grad_kernel, bool vec, RowsCfg* c) {
   c->vec = vec;
-  c->smem_bytes = (int)(3 * p.ws.Kp * sizeof(int) + (grad_kernel ? kRowsWarps * p.ws.Sp * sizeof(float) : 0));
-  if (c->smem_bytes > max_smem_optin() - 1024) {
-    set_error("Lmax=%lld needs %d bytes of shared memory in the gradient kernel", (long long)p.Lmax,
-              c->smem_bytes);
+  (void)grad_kernel;
+  const size_t per_warp = p.ws.Kp * sizeof(int);
+  int warps = (int)(kRowsSmemBudget / per_warp);
+  if (warps > kRowsMaxWarps) warps = kRowsMaxWarps;
+  if (warps < 1) {
+    set_error("Lmax=%lld needs %zu bytes of shared memory per warp", (long long)p.Lmax, per_warp);
     return B200_ERR_UNSUPPORTED_SHAPE;
   }
+  c->warps = warps;
+  c->smem_bytes = (int)(per_warp * warps);
   const int nblk = (int)((p.T + kFramesPerTask - 1) / kFramesPerTask);
-  int64_t g = (int64_t)(p.b1 - p.b0) * nblk;
+  int64_t g = ((int64_t)(p.b1 - p.b0) * nblk + warps - 1) / warps;
   const int sms = num_sms();
   if (g > sms) g = sms;
   if (g < 1) g = 1;
@@ -33,7 +41,7 @@ static int launch_rows_t(const LossParams& p, const RowsCfg& c, cudaStream_t st)
   auto kern = ctc_rows_kernel<T, VEC, GRAD>;
   if (c.smem_bytes > 48 * 1024)
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes));
-  kern<<<c.grid, kRowsWarps * 32, c.smem_bytes, st>>>(p);
+  kern<<<c.grid, c.warps * 32, c.smem_bytes, st>>>(p);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }
@@ -99,6 +107,7 @@ static LossParams make_params(const void* logits, int64_t T, int64_t B, int64_t 
   p.nll = nll;
   p.ws = carve_loss_ws(workspace, T, B, V, Lmax);
   p.b0 = 0; p.b1 = (int)B;
+  { const char* e = getenv("B200_DEBUG_VARIANT"); p.debug = e ? atoi(e) : 0; }
   return p;
 }
 
@@ -127,6 +136,21 @@ static int run_forward(LossParams p, int dtype, float* loss_sum, cudaStream_t st
       B200_CUDA(cudaFuncSetAttribute(ctc_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     dim3 grid((unsigned)(p.b1 - p.b0), 2);
     ctc_sweep_kernel<<<grid, threads, smem, st>>>(p, chf);
+    B200_CUDA(cudaGetLastError());
+  }
+  {
+    // occupancies for the backward pass (cheap, and keeps _backward a pure stream)
+    const size_t per_warp = 2 * p.ws.Kp * sizeof(int) + p.ws.Sp * sizeof(float);
+    int warps = (int)(kRowsSmemBudget / per_warp);
+    if (warps > kRowsMaxWarps) warps = kRowsMaxWarps;
+    if (warps < 1) {
+      set_error("Lmax=%lld needs %zu bytes of shared memory per warp", (long long)p.Lmax, per_warp);
+      return B200_ERR_UNSUPPORTED_SHAPE;
+    }
+    const int smem = (int)(per_warp * warps);
+    if (smem > 48 * 1024)
+      B200_CUDA(cudaFuncSetAttribute(ctc_gamma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ctc_gamma_kernel<<<cfg.grid, warps * 32, smem, st>>>(p);
     B200_CUDA(cudaGetLastError());
   }
   if (loss_sum) {

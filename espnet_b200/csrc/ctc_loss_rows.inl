@@ -1,30 +1,28 @@
 // ctc_loss_rows.inl -- the two streaming kernels of the CTC loss (included by ctc_loss.cu).
 //
-// Work unit ("task") = kFramesPerTask consecutive frames of one utterance; CTAs pull
-// tasks from an atomic counter so that ragged utterance lengths balance.  Per task the
-// utterance's labels are cached in shared memory; inside a task one warp owns one
-// (utterance, frame) row at a time.  A row is read with coalesced 128-bit
-// ld.global.nc loads, kChunkVec vectors per lane in flight, reduced in registers
-// (online log-sum-exp across chunks), and -- in the gradient kernel -- written back with
-// 128-bit streaming stores.  16 warps per SM keep >100 KB of loads in flight per SM.
+// Work unit ("task") = kFramesPerTask consecutive frames of one utterance.  Every WARP
+// pulls its own tasks from an atomic counter (ragged utterance lengths balance, and no
+// CTA-wide barrier is ever needed); the next ticket is fetched while the current task
+// runs.  A warp caches its utterance's labels in its own slice of shared memory and owns
+// one (utterance, frame) row at a time.  A row is read with coalesced 128-bit
+// ld.global.nc loads, kChunkVec vectors per lane in flight, reduced in registers (online
+// log-sum-exp across chunks) and -- in the gradient kernel -- written back with 128-bit
+// streaming stores.  Up to 24 warps per SM keep >100 KB of loads in flight per SM.
 namespace b200 {
 
-constexpr int kRowsWarps = 16;
-constexpr int kFramesPerTask = 32;
-constexpr int kChunkVec = 20;  // 16-byte vectors per lane per chunk (20*32*16 B = 10 KB per warp)
+constexpr int kRowsMaxWarps = 24;
+constexpr int kFramesPerTask = 8;
+constexpr int kChunkVec = 10;  // 16-byte vectors per lane per chunk (10*32*16 B = 5 KB per warp)
+constexpr int kGather = 5;     // label columns per lane fetched in one batch (covers L+1 <= 160)
 
 template <typename T> __device__ __forceinline__ uint32_t neg_inf_word();
 template <> __device__ __forceinline__ uint32_t neg_inf_word<float>() { return 0xff800000u; }
 template <> __device__ __forceinline__ uint32_t neg_inf_word<__nv_bfloat16>() { return 0xff80ff80u; }
 template <> __device__ __forceinline__ uint32_t neg_inf_word<__half>() { return 0xfc00fc00u; }
 
-struct RowTask {
-  int b, t0, t1;  // frames [t0, t1) of utterance b
-};
-
 // Row log2-sum-exp of x*log2(e): returns l2 such that log2 softmax(x)[v] = x[v]*log2e - l2.
 template <typename T, bool VEC>
-__device__ __forceinline__ float row_lse2(const T* __restrict__ src, int V, int nvec, int lane) {
+__device__ __forceinline__ float row_lse2(const T* __restrict__ src, int V, int nvec, int lane, int dbg = 0) {
   constexpr int PER = ElemTraits<T>::kPerVec;
   float m_run = -3.0e38f, s_run = 0.f;
   if (VEC) {
@@ -53,7 +51,7 @@ __device__ __forceinline__ float row_lse2(const T* __restrict__ src, int V, int 
         float f[PER];
         unpack16<T>(q[i], f);
 #pragma unroll
-        for (int e = 0; e < PER; ++e) s += ex2f(fmaf(f[e], B200_LOG2E, -ml));
+        for (int e = 0; e < PER; ++e) s += (dbg & 1) ? fmaf(f[e], B200_LOG2E, -ml) : ex2f(fmaf(f[e], B200_LOG2E, -ml));
       }
       s = warp_sum(s);
       s_run = s_run * ex2f((m_run - m) * B200_LOG2E) + s;
@@ -72,16 +70,18 @@ __device__ __forceinline__ float row_lse2(const T* __restrict__ src, int V, int 
   return m_run * B200_LOG2E + lg2f(s_run);
 }
 
+__device__ __forceinline__ int fetch_ticket(int* counter, int lane) {
+  int t = 0;
+  if (lane == 0) t = atomicAdd(counter, 1);
+  return __shfl_sync(0xffffffffu, t, 0);
+}
+
 template <typename T, bool VEC, bool GRAD>
-__global__ void __launch_bounds__(kRowsWarps * 32, 1) ctc_rows_kernel(LossParams p) {
+__global__ void __launch_bounds__(kRowsMaxWarps * 32, 1) ctc_rows_kernel(LossParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t Kp = p.ws.Kp, Sp = p.ws.Sp;
-  int* s_lab = reinterpret_cast<int*>(smem);              // [Kp]
-  int* s_nxt = s_lab + Kp;                                // [Kp] (GRAD)
-  int* s_fst = s_nxt + Kp;                                // [Kp] (GRAD)
-  float* gam = reinterpret_cast<float*>(s_fst + Kp) + (size_t)warp * Sp;  // [Sp] per warp (GRAD)
-  __shared__ int s_task;
+  const int64_t Kp = p.ws.Kp;
+  int* s_lab = reinterpret_cast<int*>(smem) + (size_t)warp * Kp;  // per-warp label cache
 
   const T* logits = reinterpret_cast<const T*>(p.logits);
   T* grad = reinterpret_cast<T*>(p.grad);
@@ -93,29 +93,22 @@ __global__ void __launch_bounds__(kRowsWarps * 32, 1) ctc_rows_kernel(LossParams
   int* counter = p.ws.bad + (GRAD ? 2 : 1);
   int cached_b = -1;
 
-  for (;;) {
-    __syncthreads();
-    if (threadIdx.x == 0) s_task = atomicAdd(counter, 1);
-    __syncthreads();
-    const int q = s_task;
-    if (q >= ntask) break;
+  int q = fetch_ticket(counter, lane);
+  while (q < ntask) {
+    const int q_next = fetch_ticket(counter, lane);  // overlaps with this task
     const int b = p.b0 + q / nblk;
     const int t0 = (q % nblk) * kFramesPerTask;
     const int t1 = min(t0 + kFramesPerTask, (int)p.T);
     const int Tb = (int)p.ilen[b];
     const int L = (int)p.olen[b];
+    q = q_next;
     if (!GRAD && t0 >= Tb) continue;
     if (b != cached_b && t0 < Tb) {
+      __syncwarp();
       const int* lab = p.ws.labels + (int64_t)b * Kp;
-      for (int k = threadIdx.x; k < L; k += blockDim.x) {
-        s_lab[k] = lab[k];
-        if (GRAD) {
-          s_nxt[k] = p.ws.dup_next[(int64_t)b * Kp + k];
-          s_fst[k] = p.ws.is_first[(int64_t)b * Kp + k];
-        }
-      }
+      for (int k = lane; k < L; k += 32) s_lab[k] = lab[k];
       cached_b = b;
-      __syncthreads();
+      __syncwarp();
     }
 
     float wgt = 0.f;
@@ -124,31 +117,32 @@ __global__ void __launch_bounds__(kRowsWarps * 32, 1) ctc_rows_kernel(LossParams
       if (isinf(p.ws.nll_ws[b])) wgt = __int_as_float(0x7fc00000);
     }
 
-    for (int t = t0 + warp; t < t1; t += kRowsWarps) {
+    for (int t = t0; t < t1; ++t) {
       const int64_t row = (int64_t)b * p.T + t;
       const T* src = logits + (int64_t)b * p.stride_b + (int64_t)t * p.stride_t;
+      // column of slot k: blank for k == 0, label k-1 otherwise (clamped when k > L)
+      int col[kGather];
+#pragma unroll
+      for (int i = 0; i < kGather; ++i) {
+        const int k = lane + 32 * i;
+        col[i] = (k >= 1 && k <= L) ? s_lab[k - 1] : p.blank;
+      }
       if (!GRAD) {
         if (t >= Tb) break;
-        // gather loads first: they overlap with the row stream
-        float xg[4];
-        const int ng = (L + 1 + 31) / 32;
+        // gather loads are issued first (raw, unconverted) so they overlap with the row stream
+        uint32_t raw[kGather];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int k = lane + 32 * i;
-          xg[i] = (k <= L) ? ElemTraits<T>::to_float(src[k ? s_lab[k - 1] : p.blank]) : 0.f;
-        }
-        const float l2 = row_lse2<T, VEC>(src, V, nvec, lane);
+        for (int i = 0; i < kGather; ++i) raw[i] = (p.debug & 2) ? 0u : ld_nc_raw(src + col[i]);
+        const float l2 = row_lse2<T, VEC>(src, V, nvec, lane, p.debug);
         if (lane == 0) p.ws.lse2[row] = l2;
         float* lpo = p.ws.lpg + row * Kp;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < kGather; ++i) {
           const int k = lane + 32 * i;
-          if (k <= L) lpo[k] = fmaf(xg[i], B200_LOG2E, -l2);
+          if (k <= L && !(p.debug & 4)) lpo[k] = fmaf(raw_to_float<T>(raw[i]), B200_LOG2E, -l2);
         }
-        for (int i = 4; i < ng; ++i) {
-          const int k = lane + 32 * i;
-          if (k <= L) lpo[k] = fmaf(ElemTraits<T>::to_float(src[s_lab[k - 1]]), B200_LOG2E, -l2);
-        }
+        for (int k = lane + 32 * kGather; k <= L; k += 32)
+          lpo[k] = fmaf(ElemTraits<T>::to_float(src[s_lab[k - 1]]), B200_LOG2E, -l2);
       } else {
         T* dst = grad + (int64_t)b * p.gstride_b + (int64_t)t * p.gstride_t;
         if (t >= Tb) {
@@ -162,31 +156,17 @@ __global__ void __launch_bounds__(kRowsWarps * 32, 1) ctc_rows_kernel(LossParams
           }
           continue;
         }
-        // occupancies gamma_t(s) ~ 2^(alpha + beta - lp), normalised over the row
-        const int S = 2 * L + 1;
-        const float* A = p.ws.lat + row * Sp;
-        const float* Bt = p.ws.lat + ((int64_t)p.B * p.T + row) * Sp;
-        const float* lp = p.ws.lpg + row * Kp;
-        const float l2 = p.ws.lse2[row];
-        float m = -3.0e38f;
-        for (int s = lane; s < S; s += 32) {
-          const float u = A[s] + Bt[S - 1 - s] - ((s & 1) ? lp[1 + (s >> 1)] : lp[0]);
-          gam[s] = u;
-          m = fmaxf(m, u);
+        // prologue loads (one batch): row log-sum-exp, label logits, occupancies
+        const float* occ = p.ws.occ + row * Kp;
+        const float l2 = ld_nc_f32(p.ws.lse2 + row);
+        uint32_t raw[kGather];
+        float oc[kGather];
+#pragma unroll
+        for (int i = 0; i < kGather; ++i) {
+          const int k = lane + 32 * i;
+          raw[i] = ld_nc_raw(src + col[i]);
+          oc[i] = ld_nc_f32(occ + (k <= L ? k : 0));
         }
-        m = warp_max(m);
-        float w_all = 0.f, w_blank = 0.f;
-        for (int s = lane; s < S; s += 32) {
-          const float w = ex2f(gam[s] - m);
-          gam[s] = w;
-          w_all += w;
-          if (!(s & 1)) w_blank += w;
-        }
-        w_all = warp_sum(w_all);
-        w_blank = warp_sum(w_blank);
-        const float inv = 1.0f / w_all;
-        __syncwarp();
-
         // softmax of the whole row, streamed
         if (VEC) {
           const uint4* src4 = reinterpret_cast<const uint4*>(src);
@@ -216,19 +196,20 @@ __global__ void __launch_bounds__(kRowsWarps * 32, 1) ctc_rows_kernel(LossParams
                 wgt * ex2f(fmaf(ElemTraits<T>::to_float(src[v]), B200_LOG2E, -l2)));
         }
         __syncwarp();
-        // blank and label columns: softmax - occupancy (duplicates merged in label order)
-        for (int k = lane; k < L; k += 32) {
-          if (s_fst[k]) {
-            float occ = gam[2 * k + 1];
-            for (int j = s_nxt[k]; j >= 0; j = s_nxt[j]) occ += gam[2 * j + 1];
-            const int v = s_lab[k];
-            const float xl = ElemTraits<T>::to_float(src[v]);
-            dst[v] = ElemTraits<T>::from_float(wgt * (ex2f(fmaf(xl, B200_LOG2E, -l2)) - occ * inv));
-          }
+        // blank and label columns: softmax - occupancy (occ < 0 marks a merged duplicate)
+#pragma unroll
+        for (int i = 0; i < kGather; ++i) {
+          const int k = lane + 32 * i;
+          if (k <= L && oc[i] >= 0.f)
+            dst[col[i]] = ElemTraits<T>::from_float(
+                wgt * (ex2f(fmaf(raw_to_float<T>(raw[i]), B200_LOG2E, -l2)) - oc[i]));
         }
-        if (lane == 0) {
-          const float xb = ElemTraits<T>::to_float(src[p.blank]);
-          dst[p.blank] = ElemTraits<T>::from_float(wgt * (ex2f(fmaf(xb, B200_LOG2E, -l2)) - w_blank * inv));
+        for (int k = lane + 32 * kGather; k <= L; k += 32) {
+          const float o = occ[k];
+          const int v = s_lab[k - 1];
+          if (o >= 0.f)
+            dst[v] = ElemTraits<T>::from_float(
+                wgt * (ex2f(fmaf(ElemTraits<T>::to_float(src[v]), B200_LOG2E, -l2)) - o));
         }
         __syncwarp();
       }
