@@ -1,0 +1,310 @@
+#!/usr/bin/env python
+"""bench.py -- CTC loss fwd+bwd utterances/s on B200 (BASELINE.json metric), one JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+Workload: BASELINE.json configs[1] (C2: B=64 per GPU, T=500, V=5000, L<=150, bf16 logits,
+synthetic, SURVEY.md 8d input recipe).  With N GPUs every rank takes its own 64 utterances
+(weak scaling; N=8 is config C4, global B=512) and the only collective is one 2-float NCCL
+all-reduce (sum of nll, number of utterances) per step.  A "step" is one fused
+log_softmax + CTC forward + backward over the rank's batch.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+B_PER_GPU, T, V, LMAX = 64, 500, 5000, 150
+KERNELS_PER_STEP = 6  # prep, rowstats, sweep, gamma, loss_sum, grad
+
+
+def make_batch(seed, full_length=False, dtype=torch.bfloat16):
+    from tests import _cases
+
+    return _cases.make_loss_case(B_PER_GPU, T, V, LMAX, seed=seed, dtype=dtype, full=full_length)
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons with nvidia-smi while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                f = [s.strip() for s in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.05)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(s[2 + k].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": int(self.samples[0][1]) if self.samples and self.samples[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def cpu_reference_pass(batch, n_utt, threads):
+    """The reference's CPU path for this metric: CTC.loss_fn (espnet2/asr/ctc.py:46-52) =
+    log_softmax(2) + torch.nn.CTCLoss(sum) / B, forward and backward, on the host cores."""
+    torch.set_num_threads(threads)
+    x = batch["x"][:n_utt].float()
+    ilen, olen, ys = batch["ilen"][:n_utt], batch["olen"][:n_utt], batch["ys"][:n_utt]
+    tg = torch.cat([ys[i, : olen[i]] for i in range(n_utt)])
+    crit = torch.nn.CTCLoss(reduction="sum")
+    xt = x.transpose(0, 1).detach().requires_grad_()
+    t0 = time.perf_counter()
+    loss = crit(xt.log_softmax(2), tg, ilen, olen) / xt.size(1)
+    loss.backward()
+    return time.perf_counter() - t0, float(loss.detach())
+
+
+def cpu_oracle_pass(batch, n_utt):
+    """The C restatement (oracle/ctc_oracle.c), one utterance per OpenMP thread."""
+    import numpy as np
+
+    from oracle import ctc_oracle as O
+
+    x = np.ascontiguousarray(batch["x"][:n_utt].float().numpy().transpose(1, 0, 2))
+    ys = batch["ys"][:n_utt].numpy()
+    t0 = time.perf_counter()
+    O.ctc_loss(x, ys.reshape(-1), np.arange(n_utt) * ys.shape[1], batch["ilen"][:n_utt].numpy(),
+               batch["olen"][:n_utt].numpy(), grad_scale=1.0 / n_utt)
+    return time.perf_counter() - t0, O.num_threads()
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    batch = make_batch(1236, args.full_length)
+    n_utt = 16  # bounded sample of the C2 batch per step
+    for _ in range(args.warmup):
+        cpu_reference_pass(batch, n_utt, cores)
+    t = 0.0
+    for _ in range(args.steps):
+        dt, _ = cpu_reference_pass(batch, n_utt, cores)
+        t += dt
+    value = n_utt * args.steps / t
+    sample = f"{n_utt} of the {B_PER_GPU} C2 utterances per step, fp32 copy of the bf16 logits, torch CPU"
+    line = {"impl": "reference", "metric": "ctc_loss_fwd_bwd_utterances_per_sec", "value": value,
+            "unit": "utterances/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, 1),
+            "cpu_baseline": {"value": value, "unit": "utterances/s", "cores": cores, "kind": "port",
+                             "sample": sample + " (espnet2/asr/ctc.py:46-52 restated: log_softmax + "
+                                       "torch.nn.CTCLoss(sum)/B + backward; the reference is Python and "
+                                       "cannot travel to the box)"},
+            "e2e": {"value": value, "unit": "utterances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world):
+    return {"workload": "C2: LibriSpeech-shaped CTC loss fwd+bwd, B=64 per GPU, T=500, V=5000 BPE, L<=150, "
+                        "bf16 logits" + (", all utterances full length" if args.full_length else
+                                         ", ilen~U[0.6T,T] (SURVEY 8d)"),
+            "global_batch": B_PER_GPU * world, "frames": T, "vocab": V, "max_labels": LMAX,
+            "sharding": f"utterances x{world}, 2-float NCCL all-reduce per step" if world > 1 else "single GPU",
+            "l2_policy": "inputs larger than L2 (320 MB logits + 320 MB gradient per step vs 126 MB L2)"}
+
+
+def run_b200(args, rank, world, local_rank):
+    import torch.distributed as dist
+
+    from espnet_b200 import _lib
+    from espnet_b200 import ctc_loss as CL
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+    batch = make_batch(1236 + rank, args.full_length)
+    x_host = batch["x"].pin_memory()                      # (B,T,V) bf16, what ctc_lo produces
+    x_dev = torch.empty_like(x_host, device=dev)
+    x_dev.copy_(x_host)
+    xt = x_dev.transpose(0, 1)                            # the (T,B,V) view CTC.forward hands to loss_fn
+    ys = batch["ys"].to(dev).reshape(-1)
+    off = torch.arange(B_PER_GPU) * batch["ys"].shape[1]
+    plan = CL._Plan(xt, ys, off, batch["ilen"], batch["olen"], LMAX, 0)
+    grad = CL._empty_like_strided(xt)
+    red = torch.zeros(2, device=dev)
+    gscale = 1.0 / (B_PER_GPU * world)
+
+    def step():
+        nll, ls, _ = CL.ctc_loss_fwd_bwd(xt, None, None, None, None, LMAX, grad_scale=gscale, grad_out=grad,
+                                         plan=plan)
+        if world > 1:
+            red[0:1].copy_(ls)
+            red[1] = float(B_PER_GPU)
+            dist.all_reduce(red)                          # global (sum nll, n utterances)
+            return red[0:1]
+        return ls
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    # ---- device-resident timing
+    sync_all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step()
+    e1.record()
+    sync_all()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop() if sampler else None
+    loss_value = float(loss.item())
+    value = world * B_PER_GPU * args.steps / (ms * 1e-3)
+
+    # ---- end to end through the public call with HOST buffers (pinned): H2D of the logits,
+    #      fused fwd+bwd, D2H of the loss, every step
+    sync_all()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        x_dev.copy_(x_host, non_blocking=True)
+        ls = step()
+        _ = ls.cpu()                                       # 4-byte device->host read, synchronises
+    e1.record()
+    sync_all()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    wall_e2e = time.perf_counter() - t0
+    e2e = {"value": world * B_PER_GPU * args.steps / (ms_e2e * 1e-3), "unit": "utterances/s",
+           "h2d_bytes_per_step": x_host.numel() * x_host.element_size() * world, "d2h_bytes_per_step": 4 * world,
+           "ms_per_step": ms_e2e / args.steps, "wall_ms_per_step": 1e3 * wall_e2e / args.steps}
+
+    # ---- dominant kernel (gradient stream) alone: events around b200_ctc_loss_backward
+    st = torch.cuda.current_stream().cuda_stream
+    gw = None
+
+    def bwd():
+        rc = lib.b200_ctc_loss_backward(*plan.common_args(), gw, gscale, grad.data_ptr(), grad.stride(0),
+                                        grad.stride(1), plan.ws_ptr, plan.ws_bytes, st)
+        _lib.check(rc, "b200_ctc_loss_backward")
+
+    for _ in range(3):
+        bwd()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        bwd()
+    e1.record()
+    torch.cuda.synchronize()
+    k_ms = e0.elapsed_time(e1) / args.steps
+    es = x_host.element_size()
+    k_bytes = int(batch["ilen"].sum()) * V * es + B_PER_GPU * T * V * es   # logits read (valid frames) + grad write
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["grad_kernel_dram_bytes"]
+    except Exception:
+        pass
+    achieved = k_bytes / (k_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "ctc_rows_kernel<bf16,vec,grad>", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "kernel_ms": k_ms,
+                "algorithmic_bytes": k_bytes,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)"}
+    step_bytes = 2 * B_PER_GPU * T * V * es
+    step_gbs = step_bytes * args.steps / (ms * 1e-3) / 1e9
+    roofline_step = {"algorithmic_bytes_per_gpu": step_bytes, "achieved": step_gbs, "frac": step_gbs / peak,
+                     "note": "whole step (all kernels) against logits read once + gradient written once"}
+
+    if rank != 0:
+        return
+    cpu = None
+    if world == 1:
+        cores = os.cpu_count() or 1
+        n_utt = 16
+        cpu_reference_pass(batch, 4, cores)
+        t_ref, _ = cpu_reference_pass(batch, n_utt, cores)
+        try:
+            from oracle import ctc_oracle as O
+
+            O.build()
+            t_or, thr = cpu_oracle_pass(batch, n_utt)
+            cpu = {"value": n_utt / t_or, "unit": "utterances/s", "cores": thr, "kind": "port",
+                   "sample": f"{n_utt} of the {B_PER_GPU} C2 utterances, oracle/ctc_oracle.c (double, OpenMP)",
+                   "torch_cpu": {"value": n_utt / t_ref, "cores": cores,
+                                 "what": "log_softmax + torch.nn.CTCLoss fwd+bwd (the reference's CPU path)"}}
+        except Exception as e:  # the oracle is only a reported baseline
+            cpu = {"value": n_utt / t_ref, "unit": "utterances/s", "cores": cores, "kind": "port",
+                   "sample": f"{n_utt} C2 utterances, torch CPU ctc_loss (oracle build failed: {e})"}
+    line = {"metric": "ctc_loss_fwd_bwd_utterances_per_sec", "value": value, "unit": "utterances/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16 logits, f32 lattice",
+            "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e,
+            "gpu_launches": KERNELS_PER_STEP * args.steps, "roofline": roofline, "roofline_step": roofline_step,
+            "cpu_baseline": cpu, "loss": loss_value}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--full-length", action="store_true", help="every utterance uses all T frames")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under it
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

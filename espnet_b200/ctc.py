@@ -1,0 +1,219 @@
+"""Drop-in CTC modules with ``ctc_type="b200"``.
+
+``CTC`` mirrors ``espnet2/asr/ctc.py:6-111`` and ``CTCEspnet1`` mirrors
+``espnet/nets/pytorch_backend/ctc.py:12-151`` (same constructor arguments, methods, return
+values and error behaviour); the only addition is the new ``ctc_type`` value ``"b200"``,
+which sends ``loss_fn`` through the fused sm_100a kernels instead of
+``log_softmax`` + ``torch.nn.CTCLoss``.  ``"builtin"`` is kept exactly as the reference has it
+(it is the reference's own branch and what the parity tests compare against); ``"warpctc"``
+needs the ``warpctc_pytorch`` wheel as in the reference.
+"""
+import logging
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from .ctc_loss import ctc_nll
+
+
+def _b200_loss(th_pred, targets, tgt_offsets, th_ilen, th_olen, lmax, reduce):
+    """(T,B,V) pre-softmax logits -> CTCLoss(sum|none)(log_softmax(.)) / B."""
+    nll = ctc_nll(th_pred, targets, tgt_offsets, th_ilen, th_olen, lmax, blank=0)
+    loss = nll.sum() if reduce else nll
+    return loss / th_pred.size(1)
+
+
+def _concat_offsets(th_olen, device):
+    olen = torch.as_tensor(th_olen).to(device=device, dtype=torch.int64)
+    return torch.cumsum(olen, 0) - olen
+
+
+class CTC(torch.nn.Module):
+    """CTC module (espnet2 interface).
+
+    Args:
+        odim: dimension of outputs
+        encoder_output_sizse: number of encoder projection units
+        dropout_rate: dropout rate (0.0 ~ 1.0)
+        ctc_type: b200, builtin or warpctc
+        reduce: reduce the CTC loss into a scalar
+    """
+
+    def __init__(self, odim: int, encoder_output_sizse: int, dropout_rate: float = 0.0,
+                 ctc_type: str = "b200", reduce: bool = True):
+        super().__init__()
+        eprojs = encoder_output_sizse
+        self.dropout_rate = dropout_rate
+        self.ctc_lo = torch.nn.Linear(eprojs, odim)
+        self.ctc_type = ctc_type
+
+        if self.ctc_type == "b200":
+            self.ctc_loss = None
+        elif self.ctc_type == "builtin":
+            reduction_type = "sum" if reduce else "none"
+            self.ctc_loss = torch.nn.CTCLoss(reduction=reduction_type)
+        elif self.ctc_type == "warpctc":
+            import warpctc_pytorch as warp_ctc
+
+            self.ctc_loss = warp_ctc.CTCLoss(size_average=True, reduce=reduce)
+        else:
+            raise ValueError(f'ctc_type must be "b200", "builtin" or "warpctc": {self.ctc_type}')
+
+        self.reduce = reduce
+
+    def loss_fn(self, th_pred, th_target, th_ilen, th_olen) -> torch.Tensor:
+        """th_pred (T,B,V) logits, th_target 1-D concatenated labels (espnet2/asr/ctc.py:46)."""
+        if self.ctc_type == "b200":
+            lmax = int(torch.as_tensor(th_olen).max()) if len(th_olen) else 0
+            off = _concat_offsets(th_olen, th_pred.device)
+            return _b200_loss(th_pred, th_target, off, th_ilen, th_olen, lmax, self.reduce)
+        elif self.ctc_type == "builtin":
+            th_pred = th_pred.log_softmax(2)
+            loss = self.ctc_loss(th_pred, th_target, th_ilen, th_olen)
+            # Batch-size average
+            loss = loss / th_pred.size(1)
+            return loss
+        elif self.ctc_type == "warpctc":
+            th_pred = th_pred.to(dtype=torch.float32)
+            th_target = th_target.cpu().int()
+            th_ilen = th_ilen.cpu().int()
+            th_olen = th_olen.cpu().int()
+            loss = self.ctc_loss(th_pred, th_target, th_ilen, th_olen)
+            if self.reduce:
+                loss = loss.sum()
+            return loss
+        else:
+            raise NotImplementedError
+
+    def forward(self, hs_pad, hlens, ys_pad, ys_lens):
+        """Calculate CTC loss.
+
+        Args:
+            hs_pad: batch of padded hidden state sequences (B, Tmax, D)
+            hlens: batch of lengths of hidden state sequences (B)
+            ys_pad: batch of padded character id sequence tensor (B, Lmax)
+            ys_lens: batch of lengths of character sequence (B)
+        """
+        # hs_pad: (B, L, NProj) -> ys_hat: (B, L, Nvocab) -> (L, B, Nvocab) view
+        ys_hat = self.ctc_lo(F.dropout(hs_pad, p=self.dropout_rate))
+        ys_hat = ys_hat.transpose(0, 1)
+
+        if self.ctc_type == "b200":
+            # The padded label matrix is consumed in place (row b starts at b * Lmax): no
+            # per-utterance slicing, concatenation or host synchronisation.
+            B, lmax = ys_pad.size(0), ys_pad.size(1)
+            ys_flat = ys_pad.contiguous().view(-1)
+            off = torch.arange(B, device=ys_pad.device, dtype=torch.int64) * lmax
+            loss = _b200_loss(ys_hat, ys_flat, off, hlens, ys_lens, lmax, self.reduce)
+        else:
+            # (B, L) -> (BxL,)
+            ys_true = torch.cat([ys_pad[i, :l] for i, l in enumerate(ys_lens)])
+            loss = self.loss_fn(ys_hat, ys_true, hlens, ys_lens)
+        return loss.to(device=hs_pad.device, dtype=hs_pad.dtype)
+
+    def log_softmax(self, hs_pad):
+        """log_softmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax, odim)."""
+        return F.log_softmax(self.ctc_lo(hs_pad), dim=2)
+
+    def argmax(self, hs_pad):
+        """argmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax)."""
+        return torch.argmax(self.ctc_lo(hs_pad), dim=2)
+
+
+class CTCEspnet1(torch.nn.Module):
+    """CTC module (espnet1 interface, espnet/nets/pytorch_backend/ctc.py:12).
+
+    :param int odim: dimension of outputs
+    :param int eprojs: number of encoder projection units
+    :param float dropout_rate: dropout rate (0.0 ~ 1.0)
+    :param str ctc_type: b200, builtin or warpctc
+    :param bool reduce: reduce the CTC loss into a scalar
+    """
+
+    def __init__(self, odim, eprojs, dropout_rate, ctc_type="b200", reduce=True):
+        super().__init__()
+        self.dropout_rate = dropout_rate
+        self.loss = None
+        self.ctc_lo = torch.nn.Linear(eprojs, odim)
+        self.probs = None  # for visualization
+        # the reference forces "builtin" for torch >= 1.7 when asked for warpctc
+        # (pytorch_backend/ctc.py:30-36); "b200" is never rewritten.
+        self.ctc_type = "builtin" if ctc_type == "warpctc" else ctc_type
+        if ctc_type != self.ctc_type:
+            logging.warning(f"CTC was set to {self.ctc_type} due to PyTorch version.")
+        if self.ctc_type == "b200":
+            self.ctc_loss = None
+        elif self.ctc_type == "builtin":
+            reduction_type = "sum" if reduce else "none"
+            self.ctc_loss = torch.nn.CTCLoss(reduction=reduction_type)
+        else:
+            raise ValueError('ctc_type must be "b200", "builtin" or "warpctc": {}'.format(self.ctc_type))
+        self.ignore_id = -1
+        self.reduce = reduce
+
+    def loss_fn(self, th_pred, th_target, th_ilen, th_olen):
+        if self.ctc_type == "b200":
+            lmax = int(torch.as_tensor(th_olen).max()) if len(th_olen) else 0
+            off = _concat_offsets(th_olen, th_pred.device)
+            return _b200_loss(th_pred, th_target, off, th_ilen, th_olen, lmax, self.reduce)
+        elif self.ctc_type == "builtin":
+            th_pred = th_pred.log_softmax(2)
+            with torch.backends.cudnn.flags(deterministic=True):
+                loss = self.ctc_loss(th_pred, th_target, th_ilen, th_olen)
+            loss = loss / th_pred.size(1)
+            return loss
+        else:
+            raise NotImplementedError
+
+    def forward(self, hs_pad, hlens, ys_pad):
+        """CTC forward: hs_pad (B,Tmax,D), hlens (B), ys_pad (B,Lmax) padded with -1."""
+        ys = [y[y != self.ignore_id] for y in ys_pad]  # parse padded ys
+        self.loss = None
+        hlens = torch.from_numpy(np.fromiter(hlens, dtype=np.int32))
+        olens = torch.from_numpy(np.fromiter((x.size(0) for x in ys), dtype=np.int32))
+        ys_hat = self.ctc_lo(F.dropout(hs_pad, p=self.dropout_rate))
+        ys_true = torch.cat(ys).cpu().int()  # batch x olen
+        logging.info(self.__class__.__name__ + " input lengths:  " + "".join(str(hlens).split("\n")))
+        logging.info(self.__class__.__name__ + " output lengths: " + "".join(str(olens).split("\n")))
+        dtype = ys_hat.dtype
+        ys_hat = ys_hat.transpose(0, 1)
+        if self.ctc_type == "builtin" and dtype == torch.float16:
+            # torch.ctc does not support float16 (#1751); the b200 kernels read fp16 directly
+            ys_hat = ys_hat.to(dtype=torch.float32)
+        ys_true = ys_true.to(hs_pad.device)
+        self.loss = self.loss_fn(ys_hat, ys_true, hlens, olens).to(device=hs_pad.device, dtype=dtype)
+        if self.reduce:
+            self.loss = self.loss.sum()
+            logging.info("ctc loss:" + str(float(self.loss.detach())))
+        return self.loss
+
+    def softmax(self, hs_pad):
+        """softmax of frame activations (kept for PlotCTCReport)."""
+        self.probs = F.softmax(self.ctc_lo(hs_pad), dim=2)
+        return self.probs
+
+    def log_softmax(self, hs_pad):
+        return F.log_softmax(self.ctc_lo(hs_pad), dim=2)
+
+    def argmax(self, hs_pad):
+        return torch.argmax(self.ctc_lo(hs_pad), dim=2)
+
+
+def ctc_for(args, odim, reduce=True):
+    """espnet/nets/pytorch_backend/ctc.py:219-259 with ctc_type="b200" accepted."""
+    num_encs = getattr(args, "num_encs", 1)
+    if num_encs == 1:
+        return CTCEspnet1(odim, args.eprojs, args.dropout_rate, ctc_type=args.ctc_type, reduce=reduce)
+    elif num_encs >= 1:
+        ctcs_list = torch.nn.ModuleList()
+        if args.share_ctc:
+            ctcs_list.append(CTCEspnet1(odim, args.eprojs, args.dropout_rate[0],
+                                        ctc_type=args.ctc_type, reduce=reduce))
+        else:
+            for idx in range(num_encs):
+                ctcs_list.append(CTCEspnet1(odim, args.eprojs, args.dropout_rate[idx],
+                                            ctc_type=args.ctc_type, reduce=reduce))
+        return ctcs_list
+    else:
+        raise ValueError("Number of encoders needs to be more than one. {}".format(num_encs))

@@ -1,0 +1,70 @@
+"""Host-side logic that needs no GPU: module construction, the reference-interface mirror,
+the absence of any CPU fallback on the b200 path, and the oracle quarantine."""
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from tests._util import ROOT, golden
+
+
+def test_unknown_ctc_type_raises_value_error():
+    from espnet_b200.ctc import CTC, CTCEspnet1
+
+    with pytest.raises(ValueError):
+        CTC(5, 10, ctc_type="nope")
+    with pytest.raises(ValueError):
+        CTCEspnet1(5, 10, 0.0, ctc_type="nope")
+
+
+@pytest.mark.parametrize("name", ["tiny", "v64"])
+def test_builtin_branch_reproduces_reference_loss(name):
+    """ctc_type="builtin" is the reference's own branch: same loss as the recorded one."""
+    from espnet_b200.ctc import CTC
+
+    g = golden(f"loss_{name}.npz")
+    x = torch.from_numpy(g["x"]).double()
+    ilen, olen, ys = (torch.from_numpy(g[k]) for k in ("ilen", "olen", "ys"))
+    ctc = CTC(x.shape[2], 4, ctc_type="builtin")
+    tg = torch.cat([ys[i, : olen[i]] for i in range(x.shape[0])])
+    loss = ctc.loss_fn(x.transpose(0, 1), tg, ilen, olen)
+    np.testing.assert_allclose(loss.item(), g["loss_f64"], rtol=1e-12)
+
+
+def test_b200_path_has_no_cpu_fallback():
+    from espnet_b200.ctc import CTC
+
+    ctc = CTC(7, 4, ctc_type="b200")
+    hs = torch.randn(2, 9, 4)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        ctc(hs, torch.tensor([9, 7]), torch.tensor([[1, 2], [3, 0]]), torch.tensor([2, 1]))
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    from espnet_b200 import _lib
+
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "nope.so"))
+    with pytest.raises(RuntimeError, match="no CPU or PyTorch fallback"):
+        _lib.load()
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "espnet_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".inl", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"\boracle\b", text), f"{f} mentions the oracle"
+
+
+def test_empty_like_strided_matches_ctc_lo_view():
+    from espnet_b200.ctc_loss import _empty_like_strided
+
+    x = torch.empty(3, 5, 8).transpose(0, 1)  # (T,B,V) view of (B,T,V)
+    g = _empty_like_strided(x)
+    assert g.shape == x.shape and g.stride() == x.stride()
+    y = torch.empty(5, 3, 8)
+    assert _empty_like_strided(y).stride() == y.stride()
