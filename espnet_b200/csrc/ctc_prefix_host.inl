@@ -1,0 +1,105 @@
+// ctc_prefix_host.inl -- extern "C" entry points of CTC prefix scoring.
+using namespace b200;
+
+extern "C" int b200_ctc_prefix_init(float* x, const int64_t* xlens, int64_t B, int64_t T, int64_t V, int blank,
+                                    float* r0, float* xmax, void* stream) {
+  B200_CHECK_ARG(x && xlens && r0 && xmax, B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(B >= 1 && T >= 1 && V >= 2 && B < 65536, B200_ERR_INVALID_ARGUMENT,
+                 "need 1<=B<65536, T>=1, V>=2, got B=%lld T=%lld V=%lld", (long long)B, (long long)T, (long long)V);
+  B200_CHECK_ARG(blank >= 0 && blank < V, B200_ERR_INVALID_ARGUMENT, "blank=%d outside [0,%lld)", blank,
+                 (long long)V);
+  dim3 grid((unsigned)((V + 127) / 128), (unsigned)B);
+  prefix_init_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(x, xlens, (int)T, (int)V, (int)B, blank, r0, xmax);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+extern "C" size_t b200_ctc_prefix_work_floats(int64_t T, int64_t n_bh) {
+  if (T < 1 || n_bh < 1) return 0;
+  // 2 * B*T*pad4(n_hyps) + 3*n_bh, bounded by pad4(n_hyps)*B <= 4*n_bh
+  return (size_t)(2 * T * 4 * n_bh + 4 * n_bh);
+}
+
+static int check_prefix(int64_t B, int64_t T, int64_t V, int64_t n_hyps, int blank, int64_t start, int64_t end) {
+  B200_CHECK_ARG(B >= 1 && T >= 1 && V >= 2 && B < 65536, B200_ERR_INVALID_ARGUMENT,
+                 "need 1<=B<65536, T>=1, V>=2, got B=%lld T=%lld V=%lld", (long long)B, (long long)T, (long long)V);
+  B200_CHECK_ARG(n_hyps >= 1 && n_hyps <= 32, B200_ERR_UNSUPPORTED_SHAPE,
+                 "n_hyps=%lld: 1..32 hypotheses per utterance are supported", (long long)n_hyps);
+  B200_CHECK_ARG(blank >= 0 && blank < V, B200_ERR_INVALID_ARGUMENT, "blank=%d outside [0,%lld)", blank,
+                 (long long)V);
+  B200_CHECK_ARG(start >= 1 && end <= T, B200_ERR_INVALID_ARGUMENT,
+                 "frame window [%lld,%lld) must satisfy 1 <= start, end <= T=%lld", (long long)start,
+                 (long long)end, (long long)T);
+  return B200_OK;
+}
+
+template <int NH>
+static void launch_full(const ScoreParams& p, cudaStream_t st) {
+  dim3 grid((unsigned)((p.V + kScoreThreads - 1) / kScoreThreads), (unsigned)p.B);
+  prefix_score_full_kernel<NH><<<grid, kScoreThreads, 0, st>>>(p);
+}
+
+extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const int64_t* xlens, int64_t B, int64_t T,
+                                     int64_t V, int64_t n_hyps, int blank, int eos, const float* r_prev,
+                                     const float* s_prev, const int64_t* last_ids, int64_t output_len,
+                                     const int64_t* scoring_ids, int64_t snum, int64_t start, int64_t end,
+                                     float* scores, float* log_psi, float* work, void* stream) {
+  int rc = check_prefix(B, T, V, n_hyps, blank, start, end);
+  if (rc) return rc;
+  B200_CHECK_ARG(x && xmax && xlens && r_prev && last_ids && scores && log_psi && work,
+                 B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(eos >= 0 && eos < V, B200_ERR_INVALID_ARGUMENT, "eos=%d outside [0,%lld)", eos, (long long)V);
+  B200_CHECK_ARG(snum >= 0 && (snum == 0 || scoring_ids), B200_ERR_INVALID_ARGUMENT,
+                 "snum=%lld needs scoring_ids", (long long)snum);
+  cudaStream_t st = (cudaStream_t)stream;
+  ScoreParams p;
+  p.x = x; p.xmax = xmax;
+  p.B = (int)B; p.T = (int)T; p.V = (int)V; p.n_hyps = (int)n_hyps; p.n_bh = (int)(B * n_hyps);
+  p.blank = blank; p.eos = eos;
+  p.r_prev = r_prev; p.s_prev = s_prev; p.last_ids = last_ids;
+  p.output_len = (int)output_len; p.start = (int)start; p.end = (int)end;
+  p.scoring_ids = scoring_ids; p.snum = (int)snum;
+  p.scores = scores; p.log_psi = log_psi;
+  p.w = carve_prefix(work, B, T, n_hyps);
+  prefix_phi_kernel<<<p.n_bh, 128, 0, st>>>(r_prev, xlens, (int)T, (int)n_hyps, p.n_bh, p.start, p.end, p.w);
+  B200_CUDA(cudaGetLastError());
+  if (snum == 0) {
+    if (n_hyps <= 4) launch_full<4>(p, st);
+    else if (n_hyps <= 8) launch_full<8>(p, st);
+    else if (n_hyps <= 12) launch_full<12>(p, st);
+    else if (n_hyps <= 16) launch_full<16>(p, st);
+    else launch_full<32>(p, st);
+  } else {
+    dim3 grid((unsigned)((V + 1023) / 1024), (unsigned)p.n_bh);
+    prefix_fill_kernel<<<grid, 256, 0, st>>>(p);
+    B200_CUDA(cudaGetLastError());
+    const int n = p.n_bh * p.snum;
+    prefix_score_partial_kernel<<<(n + 127) / 128, 128, 0, st>>>(p);
+  }
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+extern "C" int b200_ctc_prefix_select(const float* x, int64_t B, int64_t T, int64_t V, int64_t n_hyps, int blank,
+                                      const float* r_prev, const float* log_psi, const int64_t* last_ids,
+                                      int64_t output_len, int64_t start, int64_t end, int64_t n_bh,
+                                      const int64_t* parent, const int64_t* token, int64_t n_new,
+                                      const float* work, float* r_new, float* s_new, void* stream) {
+  (void)work;
+  B200_CHECK_ARG(x && r_prev && log_psi && last_ids && parent && token && r_new && s_new,
+                 B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(B >= 1 && T >= 1 && V >= 2 && n_hyps >= 1 && n_bh == B * n_hyps, B200_ERR_INVALID_ARGUMENT,
+                 "inconsistent sizes B=%lld n_hyps=%lld n_bh=%lld", (long long)B, (long long)n_hyps, (long long)n_bh);
+  B200_CHECK_ARG(start >= 1 && end <= T, B200_ERR_INVALID_ARGUMENT, "bad frame window [%lld,%lld)",
+                 (long long)start, (long long)end);
+  if (n_new <= 0) return B200_OK;
+  SelectParams p;
+  p.x = x; p.B = (int)B; p.T = (int)T; p.V = (int)V; p.n_hyps = (int)n_hyps; p.blank = blank;
+  p.n_bh = (int)n_bh; p.n_new = (int)n_new;
+  p.r_prev = r_prev; p.log_psi = log_psi; p.last_ids = last_ids;
+  p.output_len = (int)output_len; p.start = (int)start; p.end = (int)end;
+  p.parent = parent; p.token = token; p.r_new = r_new; p.s_new = s_new;
+  prefix_select_kernel<<<(unsigned)((n_new + 31) / 32), 32, 0, (cudaStream_t)stream>>>(p);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}

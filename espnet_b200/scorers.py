@@ -1,0 +1,103 @@
+"""CTCPrefixScorer with the B200 backend (drop-in for espnet/nets/scorers/ctc.py:11-127).
+
+Implements the reference's ``BatchPartialScorerInterface`` methods (scorer_interface.py:
+164-188) -- ``init_state``, ``select_state``, ``score_partial``, ``batch_init_state``,
+``batch_score_partial`` -- on top of :class:`CTCPrefixScoreB200`.  The per-hypothesis state
+that travels through ``BeamSearch`` / ``BatchBeamSearch`` is a small token
+``(step_state, hypothesis index, new label)``; the forward variables of all surviving
+hypotheses are materialised together, by one kernel launch, when the next scoring step needs
+them (the reference slices them one hypothesis at a time out of a (T,2,n_hyps,snum) tensor).
+"""
+import torch
+
+from .ctc_prefix_score import CTCPrefixScoreB200
+
+
+class _Survivor(object):
+    """A hypothesis that survived pruning: (state of the step, parent index, appended label)."""
+
+    __slots__ = ("step_state", "parent", "token")
+
+    def __init__(self, step_state, parent, token):
+        self.step_state = step_state
+        self.parent = int(parent)
+        self.token = int(token)
+
+
+class CTCPrefixScorer(object):
+    """Decoder interface wrapper for CTCPrefixScoreB200."""
+
+    def __init__(self, ctc: torch.nn.Module, eos: int):
+        """Initialize class.
+
+        Args:
+            ctc (torch.nn.Module): The CTC implementation (anything with ``log_softmax``), e.g.
+                :class:`espnet_b200.ctc.CTC`
+            eos (int): The end-of-sequence id.
+        """
+        self.ctc = ctc
+        self.eos = eos
+        self.impl = None
+
+    # ---- shared helpers
+    def _build(self, x):
+        logp = self.ctc.log_softmax(x.unsqueeze(0)).detach()  # assuming batch_size = 1
+        xlen = torch.tensor([logp.size(1)])
+        self.impl = CTCPrefixScoreB200(logp, xlen, 0, self.eos)
+
+    def _resolve(self, states):
+        """list of per-hypothesis states -> batch state (r_prev, s_prev, f_min, f_max) or None."""
+        if states[0] is None:
+            return None
+        step_state = states[0].step_state
+        dev = self.impl.device
+        parent = torch.tensor([s.parent for s in states], dtype=torch.int64, device=dev)
+        token = torch.tensor([s.token for s in states], dtype=torch.int64, device=dev)
+        return self.impl.select(step_state, parent, token)
+
+    # ---- BatchPartialScorerInterface
+    def batch_init_state(self, x: torch.Tensor):
+        """Get an initial state for decoding (scorers/ctc.py:88-100)."""
+        self._build(x)
+        return None
+
+    def batch_score_partial(self, y, ids, state, x):
+        """Score new tokens for a batch of hypotheses of one utterance (scorers/ctc.py:102-127).
+
+        Args:
+            y (torch.Tensor): (n_hyps, len) prefix tokens
+            ids (torch.Tensor): (n_hyps, snum) next tokens to score, or None for all
+            state: list of per-hypothesis states (from select_state) or [None, ...]
+            x (torch.Tensor): 2D encoder feature that generates ys
+        Returns:
+            (scores (n_hyps, n_vocab), batch state for select_state)
+        """
+        batch_state = self._resolve(state)
+        return self.impl(y, batch_state, ids)
+
+    def select_state(self, state, i, new_id=None):
+        """Select state with relative ids in the main beam search (scorers/ctc.py:41-64)."""
+        if type(state) == tuple:
+            if len(state) == 2:  # single-hypothesis path: (scores over ids, (step state, ids))
+                sc, (step_state, ids) = state
+                return sc[i], _Survivor(step_state, 0, ids[i])
+            return _Survivor(state, i, new_id)  # batch path (new_id > 0)
+        return None if state is None else state[i]
+
+    # ---- PartialScorerInterface (non-batch BeamSearch)
+    def init_state(self, x: torch.Tensor):
+        """Get an initial state for decoding (scorers/ctc.py:27-39)."""
+        self._build(x)
+        return 0.0, None
+
+    def score_partial(self, y, ids, state, x):
+        """Score new tokens for one hypothesis (scorers/ctc.py:66-86).
+
+        Returns (scores (len(ids),), state) where the scores are log_psi(ids) - log_psi(prefix).
+        """
+        prev_score, st = state
+        batch_state = self._resolve([st])
+        _, new_state = self.impl([[int(t) for t in y]], batch_state, ids.view(1, -1))
+        presub_score = new_state[1][0, ids.to(new_state[1].device)]
+        tscore = (presub_score - prev_score).to(device=x.device, dtype=x.dtype)
+        return tscore, (presub_score, (new_state, [int(t) for t in ids]))
