@@ -131,6 +131,63 @@ def workload_config(args, world):
             "l2_policy": "inputs larger than L2 (320 MB logits + 320 MB gradient per step vs 126 MB L2)"}
 
 
+def bench_prefix(dev, steps=20):
+    """Second half of the metric: CTC prefix-score steps/s at BASELINE config 3
+    (B=32 utterances x beam 10, T=500, V=5000, fp32 log-probs, full-vocabulary scoring as
+    recognize_beam_batch does on CUDA).  One step = __call__ + index_select_state for all 320
+    hypotheses; hypotheses advance by a seeded random walk."""
+    from espnet_b200.ctc_prefix_score import CTCPrefixScoreB200
+    from oracle.prefix_th_port import PrefixScoreEager
+
+    B, H, T_, V_ = 32, 10, 500, 5000
+    eos = V_ - 1
+    g = torch.Generator(device=dev).manual_seed(1237)
+    lp = torch.log_softmax(torch.randn(B, T_, V_, generator=g, device=dev), dim=-1)
+    gc = torch.Generator().manual_seed(1237)
+    xlens = torch.randint(300, T_ + 1, (B,), generator=gc)
+    xlens[0] = T_
+    nwalk = steps + 2
+    hyp = torch.randint(0, H, (nwalk, B, H), generator=gc)
+    tok = torch.randint(1, V_ - 1, (nwalk, B, H), generator=gc)
+    best = (hyp * V_ + tok).to(dev)
+    parents = (hyp + torch.arange(B).view(1, -1, 1) * H).view(nwalk, -1).tolist()
+    toks = tok.view(nwalk, -1).tolist()
+
+    def walk(make_impl, do_step, do_select, n):
+        impl = make_impl()
+        y = [[eos] for _ in range(B * H)]
+        state = None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for i in range(n + 1):
+            if i == 1:  # step 0 (warm-up, first label) is not timed
+                torch.cuda.synchronize()
+                e0.record()
+            st = do_step(impl, y, i, state)
+            state = do_select(impl, st, best[i])
+            y = [y[parents[i][k]] + [toks[i][k]] for k in range(B * H)]
+        e1.record()
+        torch.cuda.synchronize()
+        return n / (e0.elapsed_time(e1) * 1e-3)
+
+    ours = walk(lambda: CTCPrefixScoreB200(lp.clone(), xlens, 0, eos),
+                lambda m, y, i, s: m(y, s)[1], lambda m, st, b: m.index_select_state(st, b), steps)
+    out = {"metric": "ctc_prefix_score_steps_per_sec", "value": ours, "unit": "steps/s",
+           "config": {"workload": "C3: B=32 utterances x beam 10 (n_bh=320), T=500, V=5000, fp32 log-probs, "
+                                  "scoring_ids=None, margin=0", "steps": steps},
+           "algorithmic_bytes_per_step": 4 * (B * T_ * V_ + 2 * B * H * T_ * 2 + B * H * V_)}
+    try:
+        ref = walk(lambda: PrefixScoreEager(lp.clone(), xlens, 0, eos),
+                   lambda m, y, i, s: m.step([yi[-1] for yi in y], i, s)[1],
+                   lambda m, st, b: m.select(st, b), 3)
+        out["reference_port_gpu"] = {"value": ref, "unit": "steps/s", "kind": "port",
+                                     "what": "eager-PyTorch restatement of CTCPrefixScoreTH (oracle/prefix_th_port.py) "
+                                             "on the same GPU, 3 steps"}
+        out["speedup_vs_reference_port_gpu"] = ours / ref
+    except Exception as e:  # e.g. out of memory on a shared box
+        out["reference_port_gpu"] = {"error": str(e)[:200]}
+    return out
+
+
 def run_b200(args, rank, world, local_rank):
     import torch.distributed as dist
 
@@ -273,12 +330,17 @@ def run_b200(args, rank, world, local_rank):
         except Exception as e:  # the oracle is only a reported baseline
             cpu = {"value": n_utt / t_ref, "unit": "utterances/s", "cores": cores, "kind": "port",
                    "sample": f"{n_utt} C2 utterances, torch CPU ctc_loss (oracle build failed: {e})"}
+    prefix = None
+    if world == 1 and not args.no_prefix:
+        del grad
+        torch.cuda.empty_cache()
+        prefix = bench_prefix(dev)
     line = {"metric": "ctc_loss_fwd_bwd_utterances_per_sec", "value": value, "unit": "utterances/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16 logits, f32 lattice",
             "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e,
             "gpu_launches": KERNELS_PER_STEP * args.steps, "roofline": roofline, "roofline_step": roofline_step,
-            "cpu_baseline": cpu, "loss": loss_value}
+            "cpu_baseline": cpu, "loss": loss_value, "prefix": prefix}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -290,6 +352,7 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-prefix", action="store_true", help="skip the prefix-scoring (C3) measurement")
     ap.add_argument("--full-length", action="store_true", help="every utterance uses all T frames")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
