@@ -17,12 +17,15 @@
 
 namespace b200 {
 
+// marks a merged duplicate label in LossWs::occ (softmax - occupancy lies in [-1, 1])
+constexpr float kCorrSkip = 2.0f;
+
 struct LossWs {
   float* lse2;      // [B][T]      row log2-sum-exp (log2 units)
   float* lpg;       // [B][T][Kp]  log2-prob of blank (k=0) and label k-1 (k>=1)
   float* lat;       // [2][B][T][Sp] alpha (dir 0) and beta in reversed-state order (dir 1)
-  float* occ;       // [B][T][Kp]  occupancy of blank (k=0) / label k-1, duplicates merged into the
-                    //             first occurrence; -1 marks a later duplicate (nothing to write)
+  float* occ;       // [B][T][Kp]  softmax - occupancy of blank (k=0) / label k-1, duplicates merged into
+                    //             the first occurrence; 2.0 marks a later duplicate (nothing to write)
   int* labels;      // [B][Kp]     labels as int32
   int* dup_next;    // [B][Kp]     next position with the same label, or -1
   int* is_first;    // [B][Kp]     1 if no earlier position has the same label

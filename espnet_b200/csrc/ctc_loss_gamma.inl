@@ -4,8 +4,8 @@
 // ctc_loss_rows.inl.  gamma_t(s) ~ 2^(alpha_t(s) + beta_t(s) - lp_t(l'_s)) is normalised over
 // the row (sum_s gamma = 1 exactly in exact arithmetic, so neither the re-centring offsets
 // of the sweeps nor log p(y|x) are needed), states of the same label are merged in label
-// order (deterministic, no atomics) and the result occ[b][t][0..L] is what the gradient
-// kernel subtracts from the softmax.
+// order (deterministic, no atomics) and the result corr[b][t][0..L] = softmax - occupancy of
+// the blank and label columns is what the gradient kernel patches into the streamed softmax.
 namespace b200 {
 
 constexpr int kGammaU = 10;  // lattice states per lane loaded in one batch (covers 2L+1 <= 320)
@@ -82,14 +82,16 @@ __global__ void __launch_bounds__(kRowsMaxWarps * 32, 1) ctc_gamma_kernel(LossPa
       w_blank = warp_sum(w_blank);
       const float inv = 1.0f / w_all;
       __syncwarp();
+      // corr[k] = softmax - occupancy of column k (blank, labels); kCorrSkip marks a later
+      // duplicate of a label (its occupancy was merged into the first occurrence)
       float* out = p.ws.occ + row * Kp;
-      if (lane == 0) out[0] = w_blank * inv;
+      if (lane == 0) out[0] = ex2f(ld_nc_f32(lp)) - w_blank * inv;
       for (int k = lane; k < L; k += 32) {
-        float o = -1.0f;
+        float o = kCorrSkip;
         if (s_fst[k]) {
           o = gam[2 * k + 1];
           for (int j = s_nxt[k]; j >= 0; j = s_nxt[j]) o += gam[2 * j + 1];
-          o *= inv;
+          o = ex2f(ld_nc_f32(lp + 1 + k)) - o * inv;
         }
         out[1 + k] = o;
       }

@@ -13,14 +13,14 @@ struct RowsCfg {
 
 // Shared memory of the streaming kernels is capped so that a lattice-sweep CTA of another
 // utterance group can be resident on the same SM.
-static const int kRowsSmemBudget = 160 * 1024;
+static const int kRowsSmemBudget = 176 * 1024;
 
 static int plan_rows(const LossParams& p, bool grad_kernel, bool vec, RowsCfg* c) {
   c->vec = vec;
-  (void)grad_kernel;
-  const size_t per_warp = p.ws.Kp * sizeof(int);
+  const size_t per_warp = p.ws.Kp * sizeof(int) + (vec ? (grad_kernel ? 2 : 1) * kChunkBytes : 0);
   int warps = (int)(kRowsSmemBudget / per_warp);
-  if (warps > kRowsMaxWarps) warps = kRowsMaxWarps;
+  const int maxw = grad_kernel ? kGradMaxWarps : kRowsMaxWarps;
+  if (warps > maxw) warps = maxw;
   if (warps < 1) {
     set_error("Lmax=%lld needs %zu bytes of shared memory per warp", (long long)p.Lmax, per_warp);
     return B200_ERR_UNSUPPORTED_SHAPE;
@@ -38,10 +38,17 @@ static int plan_rows(const LossParams& p, bool grad_kernel, bool vec, RowsCfg* c
 
 template <typename T, bool VEC, bool GRAD>
 static int launch_rows_t(const LossParams& p, const RowsCfg& c, cudaStream_t st) {
-  auto kern = ctc_rows_kernel<T, VEC, GRAD>;
-  if (c.smem_bytes > 48 * 1024)
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes));
-  kern<<<c.grid, c.warps * 32, c.smem_bytes, st>>>(p);
+  if (GRAD) {
+    auto kern = ctc_grad_kernel<T, VEC>;
+    if (c.smem_bytes > 48 * 1024)
+      B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes));
+    kern<<<c.grid, c.warps * 32, c.smem_bytes, st>>>(p);
+  } else {
+    auto kern = ctc_rowstats_kernel<T, VEC>;
+    if (c.smem_bytes > 48 * 1024)
+      B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes));
+    kern<<<c.grid, c.warps * 32, c.smem_bytes, st>>>(p);
+  }
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }

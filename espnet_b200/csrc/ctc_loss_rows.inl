@@ -1,73 +1,72 @@
 // ctc_loss_rows.inl -- the two streaming kernels of the CTC loss (included by ctc_loss.cu).
 //
-// Work unit ("task") = kFramesPerTask consecutive frames of one utterance.  Every WARP
-// pulls its own tasks from an atomic counter (ragged utterance lengths balance, and no
-// CTA-wide barrier is ever needed); the next ticket is fetched while the current task
-// runs.  A warp caches its utterance's labels in its own slice of shared memory and owns
-// one (utterance, frame) row at a time.  A row is read with coalesced 128-bit
-// ld.global.nc loads, kChunkVec vectors per lane in flight, reduced in registers (online
-// log-sum-exp across chunks) and -- in the gradient kernel -- written back with 128-bit
-// streaming stores.  Up to 24 warps per SM keep >100 KB of loads in flight per SM.
+// Work unit ("task") = kFramesPerTask consecutive frames of one utterance.  Every WARP pulls
+// its own tasks from an atomic counter (ragged utterance lengths balance, no CTA-wide
+// barrier).  A warp caches its utterance's labels in its slice of shared memory and owns one
+// (utterance, frame) row at a time.  A row is read in chunks of kChunkVec 16-byte vectors per
+// lane with coalesced ld.global.nc loads (5 KB in flight per warp).
+//
+//   rowstats: max (packed bf16/fp16 max for half types) and sum-exp in registers, online
+//             across chunks; each chunk is also stashed in the warp's shared-memory buffer so
+//             that the blank/label columns are gathered from shared memory, not from HBM.
+//   grad:     softmax * weight (the weight is folded into the exponent), packed to the output
+//             dtype into the warp's shared-memory buffer, blank/label columns patched there
+//             with the pre-computed (softmax - occupancy), and the chunk leaves with ONE bulk
+//             shared->global copy (cp.async.bulk, SASS UBLKCP) per 5 KB.
 namespace b200 {
 
 constexpr int kRowsMaxWarps = 24;
+constexpr int kGradMaxWarps = 16;
 constexpr int kFramesPerTask = 8;
-constexpr int kChunkVec = 10;  // 16-byte vectors per lane per chunk (10*32*16 B = 5 KB per warp)
-constexpr int kGather = 5;     // label columns per lane fetched in one batch (covers L+1 <= 160)
+constexpr int kChunkVec = 10;              // 16-byte vectors per lane per chunk
+constexpr int kChunkBytes = kChunkVec * 32 * 16;
+constexpr int kGather = 5;                 // label slots per lane held in registers (L+1 <= 160)
 
 template <typename T> __device__ __forceinline__ uint32_t neg_inf_word();
 template <> __device__ __forceinline__ uint32_t neg_inf_word<float>() { return 0xff800000u; }
 template <> __device__ __forceinline__ uint32_t neg_inf_word<__nv_bfloat16>() { return 0xff80ff80u; }
 template <> __device__ __forceinline__ uint32_t neg_inf_word<__half>() { return 0xfc00fc00u; }
 
-// Row log2-sum-exp of x*log2(e): returns l2 such that log2 softmax(x)[v] = x[v]*log2e - l2.
-template <typename T, bool VEC>
-__device__ __forceinline__ float row_lse2(const T* __restrict__ src, int V, int nvec, int lane, int dbg = 0) {
-  constexpr int PER = ElemTraits<T>::kPerVec;
-  float m_run = -3.0e38f, s_run = 0.f;
-  if (VEC) {
-    const uint4* src4 = reinterpret_cast<const uint4*>(src);
-    for (int c0 = 0; c0 < nvec; c0 += 32 * kChunkVec) {
-      uint4 q[kChunkVec];
-      const uint32_t ni = neg_inf_word<T>();
+// max over the elements of a chunk held in registers
+template <typename T>
+__device__ __forceinline__ float chunk_max(const uint4 (&q)[kChunkVec]);
+template <>
+__device__ __forceinline__ float chunk_max<float>(const uint4 (&q)[kChunkVec]) {
+  float m0 = -3.0e38f, m1 = -3.0e38f;
 #pragma unroll
-      for (int i = 0; i < kChunkVec; ++i) {
-        const int j = c0 + lane + 32 * i;
-        q[i] = j < nvec ? ld_nc_v4(src4 + j) : make_uint4(ni, ni, ni, ni);
-      }
-      float m = -3.0e38f;
-#pragma unroll
-      for (int i = 0; i < kChunkVec; ++i) {
-        float f[PER];
-        unpack16<T>(q[i], f);
-#pragma unroll
-        for (int e = 0; e < PER; ++e) m = fmaxf(m, f[e]);
-      }
-      m = fmaxf(warp_max(m), m_run);
-      const float ml = m * B200_LOG2E;
-      float s = 0.f;
-#pragma unroll
-      for (int i = 0; i < kChunkVec; ++i) {
-        float f[PER];
-        unpack16<T>(q[i], f);
-#pragma unroll
-        for (int e = 0; e < PER; ++e) s += (dbg & 1) ? fmaf(f[e], B200_LOG2E, -ml) : ex2f(fmaf(f[e], B200_LOG2E, -ml));
-      }
-      s = warp_sum(s);
-      s_run = s_run * ex2f((m_run - m) * B200_LOG2E) + s;
-      m_run = m;
-    }
-  } else {
-    float m = -3.0e38f;
-    for (int v = lane; v < V; v += 32) m = fmaxf(m, ElemTraits<T>::to_float(src[v]));
-    m = warp_max(m);
-    const float ml = m * B200_LOG2E;
-    float s = 0.f;
-    for (int v = lane; v < V; v += 32) s += ex2f(fmaf(ElemTraits<T>::to_float(src[v]), B200_LOG2E, -ml));
-    s_run = warp_sum(s);
-    m_run = m;
+  for (int i = 0; i < kChunkVec; ++i) {
+    m0 = fmaxf(m0, fmaxf(__uint_as_float(q[i].x), __uint_as_float(q[i].y)));
+    m1 = fmaxf(m1, fmaxf(__uint_as_float(q[i].z), __uint_as_float(q[i].w)));
   }
-  return m_run * B200_LOG2E + lg2f(s_run);
+  return fmaxf(m0, m1);
+}
+template <>
+__device__ __forceinline__ float chunk_max<__nv_bfloat16>(const uint4 (&q)[kChunkVec]) {
+  __nv_bfloat162 m0 = *reinterpret_cast<const __nv_bfloat162*>(&q[0].x);
+  __nv_bfloat162 m1 = *reinterpret_cast<const __nv_bfloat162*>(&q[0].y);
+#pragma unroll
+  for (int i = 0; i < kChunkVec; ++i) {
+    m0 = __hmax2(m0, *reinterpret_cast<const __nv_bfloat162*>(&q[i].x));
+    m1 = __hmax2(m1, *reinterpret_cast<const __nv_bfloat162*>(&q[i].y));
+    m0 = __hmax2(m0, *reinterpret_cast<const __nv_bfloat162*>(&q[i].z));
+    m1 = __hmax2(m1, *reinterpret_cast<const __nv_bfloat162*>(&q[i].w));
+  }
+  m0 = __hmax2(m0, m1);
+  return fmaxf(__low2float(m0), __high2float(m0));
+}
+template <>
+__device__ __forceinline__ float chunk_max<__half>(const uint4 (&q)[kChunkVec]) {
+  __half2 m0 = *reinterpret_cast<const __half2*>(&q[0].x);
+  __half2 m1 = *reinterpret_cast<const __half2*>(&q[0].y);
+#pragma unroll
+  for (int i = 0; i < kChunkVec; ++i) {
+    m0 = __hmax2(m0, *reinterpret_cast<const __half2*>(&q[i].x));
+    m1 = __hmax2(m1, *reinterpret_cast<const __half2*>(&q[i].y));
+    m0 = __hmax2(m0, *reinterpret_cast<const __half2*>(&q[i].z));
+    m1 = __hmax2(m1, *reinterpret_cast<const __half2*>(&q[i].w));
+  }
+  m0 = __hmax2(m0, m1);
+  return fmaxf(__low2float(m0), __high2float(m0));
 }
 
 __device__ __forceinline__ int fetch_ticket(int* counter, int lane) {
@@ -76,145 +75,278 @@ __device__ __forceinline__ int fetch_ticket(int* counter, int lane) {
   return __shfl_sync(0xffffffffu, t, 0);
 }
 
-template <typename T, bool VEC, bool GRAD>
-__global__ void __launch_bounds__(kRowsMaxWarps * 32, 1) ctc_rows_kernel(LossParams p) {
+struct RowTask {
+  int b, t0, t1, Tb, L;
+};
+
+// Pulls the next task; returns false when the queue is exhausted.
+__device__ __forceinline__ bool next_task(const LossParams& p, int* counter, int lane, int nblk, int ntask,
+                                          RowTask* k) {
+  const int q = fetch_ticket(counter, lane);
+  if (q >= ntask) return false;
+  k->b = p.b0 + q / nblk;
+  k->t0 = (q % nblk) * kFramesPerTask;
+  k->t1 = min(k->t0 + kFramesPerTask, (int)p.T);
+  k->Tb = (int)p.ilen[k->b];
+  k->L = (int)p.olen[k->b];
+  return true;
+}
+
+// ---------------------------------------------------------------------------- rowstats
+template <typename T, bool VEC>
+__global__ void __launch_bounds__(kRowsMaxWarps * 32, 1) ctc_rowstats_kernel(LossParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t Kp = p.ws.Kp;
-  int* s_lab = reinterpret_cast<int*>(smem) + (size_t)warp * Kp;  // per-warp label cache
+  const size_t per_warp = Kp * sizeof(int) + (VEC ? kChunkBytes : 0);
+  int* s_lab = reinterpret_cast<int*>(smem + warp * per_warp);
+  uint4* buf4 = reinterpret_cast<uint4*>(s_lab + Kp);
+  const T* bufT = reinterpret_cast<const T*>(buf4);
+
+  const T* logits = reinterpret_cast<const T*>(p.logits);
+  const int V = (int)p.V;
+  const int nvec = (int)((int64_t)V * sizeof(T) / 16);
+  constexpr int PER = ElemTraits<T>::kPerVec;
+  constexpr int CHUNK_ELEMS = kChunkVec * 32 * PER;
+  const int nblk = (int)((p.T + kFramesPerTask - 1) / kFramesPerTask);
+  const int ntask = (p.b1 - p.b0) * nblk;
+  int* counter = p.ws.bad + 1;
+  int cached_b = -1;
+  RowTask k;
+
+  while (next_task(p, counter, lane, nblk, ntask, &k)) {
+    if (k.t0 >= k.Tb) continue;
+    const int L = k.L;
+    if (k.b != cached_b) {
+      __syncwarp();
+      const int* lab = p.ws.labels + (int64_t)k.b * Kp;
+      for (int i = lane; i < L; i += 32) s_lab[i] = lab[i];
+      cached_b = k.b;
+      __syncwarp();
+    }
+    int col[kGather];
+#pragma unroll
+    for (int i = 0; i < kGather; ++i) {
+      const int kk = lane + 32 * i;
+      col[i] = (kk >= 1 && kk <= L) ? s_lab[kk - 1] : p.blank;
+    }
+    const int t_end = min(k.t1, k.Tb);
+    for (int t = k.t0; t < t_end; ++t) {
+      const int64_t row = (int64_t)k.b * p.T + t;
+      const T* src = logits + (int64_t)k.b * p.stride_b + (int64_t)t * p.stride_t;
+      float* lpo = p.ws.lpg + row * Kp;
+      float xg[kGather];
+#pragma unroll
+      for (int i = 0; i < kGather; ++i) xg[i] = 0.f;
+      float m_run = -3.0e38f, s_run = 0.f;
+      if (VEC) {
+        const uint4* src4 = reinterpret_cast<const uint4*>(src);
+        for (int c0 = 0; c0 < nvec; c0 += 32 * kChunkVec) {
+          uint4 q[kChunkVec];
+          const uint32_t ni = neg_inf_word<T>();
+#pragma unroll
+          for (int i = 0; i < kChunkVec; ++i) {
+            const int j = c0 + lane + 32 * i;
+            q[i] = j < nvec ? ld_nc_v4(src4 + j) : make_uint4(ni, ni, ni, ni);
+          }
+          // stash the chunk: the blank/label columns are gathered from shared memory
+#pragma unroll
+          for (int i = 0; i < kChunkVec; ++i) buf4[lane + 32 * i] = q[i];
+          const float m = fmaxf(warp_max(chunk_max<T>(q)), m_run);
+          const float ml = m * B200_LOG2E;
+          float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+          for (int i = 0; i < kChunkVec; ++i) {
+            float f[PER];
+            unpack16<T>(q[i], f);
+#pragma unroll
+            for (int e = 0; e < PER; e += 2) {
+              s0 += ex2f(fmaf(f[e], B200_LOG2E, -ml));
+              s1 += ex2f(fmaf(f[e + 1], B200_LOG2E, -ml));
+            }
+          }
+          const float s = warp_sum(s0 + s1);
+          s_run = s_run * ex2f((m_run - m) * B200_LOG2E) + s;
+          m_run = m;
+          __syncwarp();
+          const int lo = c0 * PER, hi = lo + CHUNK_ELEMS;
+#pragma unroll
+          for (int i = 0; i < kGather; ++i)
+            if (col[i] >= lo && col[i] < hi) xg[i] = ElemTraits<T>::to_float(bufT[col[i] - lo]);
+          for (int kk = lane + 32 * kGather; kk <= L; kk += 32) {  // L+1 > 160: spill to lpg directly
+            const int v = s_lab[kk - 1];
+            if (v >= lo && v < hi) lpo[kk] = ElemTraits<T>::to_float(bufT[v - lo]) * B200_LOG2E;
+          }
+          __syncwarp();
+        }
+      } else {
+        float m = -3.0e38f;
+        for (int v = lane; v < V; v += 32) m = fmaxf(m, ElemTraits<T>::to_float(src[v]));
+        m = warp_max(m);
+        const float ml = m * B200_LOG2E;
+        float s = 0.f;
+        for (int v = lane; v < V; v += 32) s += ex2f(fmaf(ElemTraits<T>::to_float(src[v]), B200_LOG2E, -ml));
+        s_run = warp_sum(s);
+        m_run = m;
+#pragma unroll
+        for (int i = 0; i < kGather; ++i) xg[i] = ElemTraits<T>::to_float(src[col[i]]);
+        for (int kk = lane + 32 * kGather; kk <= L; kk += 32)
+          lpo[kk] = ElemTraits<T>::to_float(src[s_lab[kk - 1]]) * B200_LOG2E;
+      }
+      const float l2 = m_run * B200_LOG2E + lg2f(s_run);
+      if (lane == 0) p.ws.lse2[row] = l2;
+#pragma unroll
+      for (int i = 0; i < kGather; ++i) {
+        const int kk = lane + 32 * i;
+        if (kk <= L) lpo[kk] = fmaf(xg[i], B200_LOG2E, -l2);
+      }
+      for (int kk = lane + 32 * kGather; kk <= L; kk += 32) lpo[kk] -= l2;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------- gradient
+template <typename T> __device__ __forceinline__ uint32_t nan_word();
+template <> __device__ __forceinline__ uint32_t nan_word<float>() { return 0x7fc00000u; }
+template <> __device__ __forceinline__ uint32_t nan_word<__nv_bfloat16>() { return 0x7fc07fc0u; }
+template <> __device__ __forceinline__ uint32_t nan_word<__half>() { return 0x7e007e00u; }
+template <typename T> __device__ __forceinline__ uint32_t sign_word();
+template <> __device__ __forceinline__ uint32_t sign_word<float>() { return 0x80000000u; }
+template <> __device__ __forceinline__ uint32_t sign_word<__nv_bfloat16>() { return 0x80008000u; }
+template <> __device__ __forceinline__ uint32_t sign_word<__half>() { return 0x80008000u; }
+
+template <typename T, bool VEC>
+__global__ void __launch_bounds__(kGradMaxWarps * 32, 1) ctc_grad_kernel(LossParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t Kp = p.ws.Kp;
+  const size_t per_warp = Kp * sizeof(int) + (VEC ? 2 * kChunkBytes : 0);
+  int* s_lab = reinterpret_cast<int*>(smem + warp * per_warp);
+  unsigned char* obuf = reinterpret_cast<unsigned char*>(s_lab + Kp);
 
   const T* logits = reinterpret_cast<const T*>(p.logits);
   T* grad = reinterpret_cast<T*>(p.grad);
   const int V = (int)p.V;
   const int nvec = (int)((int64_t)V * sizeof(T) / 16);
   constexpr int PER = ElemTraits<T>::kPerVec;
+  constexpr int CHUNK_ELEMS = kChunkVec * 32 * PER;
   const int nblk = (int)((p.T + kFramesPerTask - 1) / kFramesPerTask);
   const int ntask = (p.b1 - p.b0) * nblk;
-  int* counter = p.ws.bad + (GRAD ? 2 : 1);
+  int* counter = p.ws.bad + 2;
   int cached_b = -1;
+  uint32_t nbuf = 0;  // chunks stored so far by this warp (selects the output buffer)
+  RowTask k;
 
-  int q = fetch_ticket(counter, lane);
-  while (q < ntask) {
-    const int q_next = fetch_ticket(counter, lane);  // overlaps with this task
-    const int b = p.b0 + q / nblk;
-    const int t0 = (q % nblk) * kFramesPerTask;
-    const int t1 = min(t0 + kFramesPerTask, (int)p.T);
-    const int Tb = (int)p.ilen[b];
-    const int L = (int)p.olen[b];
-    q = q_next;
-    if (!GRAD && t0 >= Tb) continue;
-    if (b != cached_b && t0 < Tb) {
+  while (next_task(p, counter, lane, nblk, ntask, &k)) {
+    const int L = k.L;
+    if (k.b != cached_b && k.t0 < k.Tb) {
       __syncwarp();
-      const int* lab = p.ws.labels + (int64_t)b * Kp;
-      for (int k = lane; k < L; k += 32) s_lab[k] = lab[k];
-      cached_b = b;
+      const int* lab = p.ws.labels + (int64_t)k.b * Kp;
+      for (int i = lane; i < L; i += 32) s_lab[i] = lab[i];
+      cached_b = k.b;
       __syncwarp();
     }
-
-    float wgt = 0.f;
-    if (GRAD) {
-      wgt = p.grad_scale * (p.grad_weight ? p.grad_weight[b] : 1.0f);
-      if (isinf(p.ws.nll_ws[b])) wgt = __int_as_float(0x7fc00000);
+    int col[kGather];
+#pragma unroll
+    for (int i = 0; i < kGather; ++i) {
+      const int kk = lane + 32 * i;
+      col[i] = (k.t0 < k.Tb && kk >= 1 && kk <= L) ? s_lab[kk - 1] : p.blank;
     }
+    const float wgt = p.grad_scale * (p.grad_weight ? p.grad_weight[k.b] : 1.0f);
+    const bool poison = isinf(p.ws.nll_ws[k.b]) || isnan(wgt);  // infeasible utterance: NaN rows (torch)
+    const bool neg = wgt < 0.f;
+    const float lw = lg2f(fabsf(wgt));  // weight folded into the exponent; -inf for wgt == 0
 
-    for (int t = t0; t < t1; ++t) {
-      const int64_t row = (int64_t)b * p.T + t;
-      const T* src = logits + (int64_t)b * p.stride_b + (int64_t)t * p.stride_t;
-      // column of slot k: blank for k == 0, label k-1 otherwise (clamped when k > L)
-      int col[kGather];
+    for (int t = k.t0; t < k.t1; ++t) {
+      const int64_t row = (int64_t)k.b * p.T + t;
+      const T* src = logits + (int64_t)k.b * p.stride_b + (int64_t)t * p.stride_t;
+      T* dst = grad + (int64_t)k.b * p.gstride_b + (int64_t)t * p.gstride_t;
+      if (t >= k.Tb) {
+        // frames past the end of the utterance: zero gradient
+        if (VEC) {
+          uint4* d4 = reinterpret_cast<uint4*>(dst);
+          const uint4 z = make_uint4(0, 0, 0, 0);
+          for (int j = lane; j < nvec; j += 32) st_cs_v4(d4 + j, z);
+        } else {
+          for (int v = lane; v < V; v += 32) dst[v] = ElemTraits<T>::from_float(0.f);
+        }
+        continue;
+      }
+      const float* corr = p.ws.occ + row * Kp;
+      const float l2w = ld_nc_f32(p.ws.lse2 + row) - lw;
+      float cr[kGather];
 #pragma unroll
       for (int i = 0; i < kGather; ++i) {
-        const int k = lane + 32 * i;
-        col[i] = (k >= 1 && k <= L) ? s_lab[k - 1] : p.blank;
+        const int kk = lane + 32 * i;
+        cr[i] = ld_nc_f32(corr + (kk <= L ? kk : 0));
       }
-      if (!GRAD) {
-        if (t >= Tb) break;
-        // gather loads are issued first (raw, unconverted) so they overlap with the row stream
-        uint32_t raw[kGather];
+      if (VEC) {
+        const uint4* src4 = reinterpret_cast<const uint4*>(src);
+        for (int c0 = 0; c0 < nvec; c0 += 32 * kChunkVec) {
+          unsigned char* buf = obuf + (nbuf & 1) * kChunkBytes;
+          ++nbuf;
+          uint4 q[kChunkVec];
 #pragma unroll
-        for (int i = 0; i < kGather; ++i) raw[i] = (p.debug & 2) ? 0u : ld_nc_raw(src + col[i]);
-        const float l2 = row_lse2<T, VEC>(src, V, nvec, lane, p.debug);
-        if (lane == 0) p.ws.lse2[row] = l2;
-        float* lpo = p.ws.lpg + row * Kp;
+          for (int i = 0; i < kChunkVec; ++i) {
+            const int j = c0 + lane + 32 * i;
+            q[i] = j < nvec ? ld_nc_v4(src4 + j) : make_uint4(0, 0, 0, 0);
+          }
+          // the bulk store that last used this buffer (two chunks ago) must have read it
+          if (lane == 0) bulk_wait_read<1>();
+          __syncwarp();
+          uint4* b4 = reinterpret_cast<uint4*>(buf);
 #pragma unroll
-        for (int i = 0; i < kGather; ++i) {
-          const int k = lane + 32 * i;
-          if (k <= L && !(p.debug & 4)) lpo[k] = fmaf(raw_to_float<T>(raw[i]), B200_LOG2E, -l2);
+          for (int i = 0; i < kChunkVec; ++i) {
+            float f[PER];
+            unpack16<T>(q[i], f);
+#pragma unroll
+            for (int e = 0; e < PER; ++e) f[e] = ex2f(fmaf(f[e], B200_LOG2E, -l2w));
+            uint4 o = pack16<T>(f);
+            if (neg) { const uint32_t sw = sign_word<T>(); o.x ^= sw; o.y ^= sw; o.z ^= sw; o.w ^= sw; }
+            if (poison) { const uint32_t nw = nan_word<T>(); o = make_uint4(nw, nw, nw, nw); }
+            b4[lane + 32 * i] = o;
+          }
+          __syncwarp();
+          // blank and label columns: weight * (softmax - occupancy), duplicates already merged
+          const int lo = c0 * PER, hi = lo + CHUNK_ELEMS;
+          T* bT = reinterpret_cast<T*>(buf);
+          if (!poison) {
+#pragma unroll
+            for (int i = 0; i < kGather; ++i) {
+              const int kk = lane + 32 * i;
+              if (kk <= L && cr[i] < 1.5f && col[i] >= lo && col[i] < hi)
+                bT[col[i] - lo] = ElemTraits<T>::from_float(wgt * cr[i]);
+            }
+            for (int kk = lane + 32 * kGather; kk <= L; kk += 32) {
+              const int v = s_lab[kk - 1];
+              const float c = corr[kk];
+              if (c < 1.5f && v >= lo && v < hi) bT[v - lo] = ElemTraits<T>::from_float(wgt * c);
+            }
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            const int bytes = min(kChunkBytes, (nvec - c0) * 16);
+            bulk_s2g(reinterpret_cast<unsigned char*>(dst) + (size_t)c0 * 16, buf, (uint32_t)bytes);
+            bulk_commit();
+          }
         }
-        for (int k = lane + 32 * kGather; k <= L; k += 32)
-          lpo[k] = fmaf(ElemTraits<T>::to_float(src[s_lab[k - 1]]), B200_LOG2E, -l2);
       } else {
-        T* dst = grad + (int64_t)b * p.gstride_b + (int64_t)t * p.gstride_t;
-        if (t >= Tb) {
-          // frames past the end of the utterance: zero gradient
-          if (VEC) {
-            uint4* d4 = reinterpret_cast<uint4*>(dst);
-            const uint4 z = make_uint4(0, 0, 0, 0);
-            for (int j = lane; j < nvec; j += 32) st_cs_v4(d4 + j, z);
-          } else {
-            for (int v = lane; v < V; v += 32) dst[v] = ElemTraits<T>::from_float(0.f);
-          }
-          continue;
-        }
-        // prologue loads (one batch): row log-sum-exp, label logits, occupancies
-        const float* occ = p.ws.occ + row * Kp;
-        const float l2 = ld_nc_f32(p.ws.lse2 + row);
-        uint32_t raw[kGather];
-        float oc[kGather];
-#pragma unroll
-        for (int i = 0; i < kGather; ++i) {
-          const int k = lane + 32 * i;
-          raw[i] = ld_nc_raw(src + col[i]);
-          oc[i] = ld_nc_f32(occ + (k <= L ? k : 0));
-        }
-        // softmax of the whole row, streamed
-        if (VEC) {
-          const uint4* src4 = reinterpret_cast<const uint4*>(src);
-          uint4* d4 = reinterpret_cast<uint4*>(dst);
-          for (int c0 = 0; c0 < nvec; c0 += 32 * kChunkVec) {
-            uint4 qv[kChunkVec];
-#pragma unroll
-            for (int i = 0; i < kChunkVec; ++i) {
-              const int j = c0 + lane + 32 * i;
-              if (j < nvec) qv[i] = ld_nc_v4(src4 + j);
-            }
-#pragma unroll
-            for (int i = 0; i < kChunkVec; ++i) {
-              const int j = c0 + lane + 32 * i;
-              if (j < nvec) {
-                float f[PER];
-                unpack16<T>(qv[i], f);
-#pragma unroll
-                for (int e = 0; e < PER; ++e) f[e] = wgt * ex2f(fmaf(f[e], B200_LOG2E, -l2));
-                st_cs_v4(d4 + j, pack16<T>(f));
-              }
-            }
-          }
-        } else {
-          for (int v = lane; v < V; v += 32)
-            dst[v] = ElemTraits<T>::from_float(
-                wgt * ex2f(fmaf(ElemTraits<T>::to_float(src[v]), B200_LOG2E, -l2)));
-        }
+        const float w = poison ? __int_as_float(0x7fc00000) : wgt;
+        const float l2 = p.ws.lse2[row];
+        for (int v = lane; v < V; v += 32)
+          dst[v] = ElemTraits<T>::from_float(w * ex2f(fmaf(ElemTraits<T>::to_float(src[v]), B200_LOG2E, -l2)));
         __syncwarp();
-        // blank and label columns: softmax - occupancy (occ < 0 marks a merged duplicate)
-#pragma unroll
-        for (int i = 0; i < kGather; ++i) {
-          const int k = lane + 32 * i;
-          if (k <= L && oc[i] >= 0.f)
-            dst[col[i]] = ElemTraits<T>::from_float(
-                wgt * (ex2f(fmaf(raw_to_float<T>(raw[i]), B200_LOG2E, -l2)) - oc[i]));
-        }
-        for (int k = lane + 32 * kGather; k <= L; k += 32) {
-          const float o = occ[k];
-          const int v = s_lab[k - 1];
-          if (o >= 0.f)
-            dst[v] = ElemTraits<T>::from_float(
-                wgt * (ex2f(fmaf(ElemTraits<T>::to_float(src[v]), B200_LOG2E, -l2)) - o));
+        for (int kk = lane; kk <= L; kk += 32) {
+          const float c = corr[kk];
+          const int v = kk ? s_lab[kk - 1] : p.blank;
+          if (c < 1.5f) dst[v] = ElemTraits<T>::from_float(w * c);
         }
         __syncwarp();
       }
     }
   }
+  if (VEC && lane == 0) bulk_wait_all<0>();
 }
 
 }  // namespace b200
