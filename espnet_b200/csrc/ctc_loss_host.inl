@@ -133,18 +133,8 @@ static int run_forward(LossParams p, int dtype, float* loss_sum, cudaStream_t st
   }
   rc = launch_rows<false>(p, dtype, cfg, st);
   if (rc) return rc;
-  {
-    const int threads = (int)align_up((size_t)(p.Lmax + 1), 32);
-    int chf = (int)(16384 / (p.ws.Kp * sizeof(float)));
-    if (chf > kSweepMaxChf) chf = kSweepMaxChf;
-    if (chf < 1) chf = 1;
-    const int smem = 128 + kSweepRing * chf * (int)p.ws.Kp * (int)sizeof(float);
-    if (smem > 48 * 1024)
-      B200_CUDA(cudaFuncSetAttribute(ctc_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    dim3 grid((unsigned)(p.b1 - p.b0), 2);
-    ctc_sweep_kernel<<<grid, threads, smem, st>>>(p, chf);
-    B200_CUDA(cudaGetLastError());
-  }
+  rc = launch_sweep(p, st);
+  if (rc) return rc;
   {
     // occupancies for the backward pass (cheap, and keeps _backward a pure stream)
     const size_t per_warp = 2 * p.ws.Kp * sizeof(int) + p.ws.Sp * sizeof(float);
