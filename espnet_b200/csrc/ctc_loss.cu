@@ -25,16 +25,20 @@ __global__ void ctc_prep_kernel(LossParams p) {
     lab[i] = (int)v;
   }
   __syncthreads();
+  int* dc = p.ws.dupcode + (int64_t)b * p.ws.Kp;
   for (int64_t i = threadIdx.x; i < L; i += blockDim.x) {
     const int v = s_lab[i];
-    int first = 1;
-    for (int64_t j = 0; j < i; ++j)
-      if (s_lab[j] == v) { first = 0; break; }
-    int n = -1;
-    for (int64_t j = i + 1; j < L; ++j)
-      if (s_lab[j] == v) { n = (int)j; break; }
+    // branch-free scan (every thread reads the same word: a broadcast)
+    int first = 1, n = 0x7fffffff;
+    for (int j = 0; j < (int)L; ++j) {
+      const bool same = s_lab[j] == v;
+      if (same && j < (int)i) first = 0;
+      if (same && j > (int)i) n = min(n, j);
+    }
+    if (n == 0x7fffffff) n = -1;
     fst[i] = first;
     nxt[i] = n;
+    dc[i] = (first ? 0 : kDupLater) | (n + 1);
   }
 }
 
@@ -50,5 +54,6 @@ __global__ void ctc_loss_sum_kernel(const float* nll, int B, float* out) {
 
 #include "ctc_loss_sweep.inl"
 #include "ctc_loss_rows.inl"
-#include "ctc_loss_gamma.inl"
+#include "ctc_loss_occ.inl"
+#include "ctc_loss_stream.inl"
 #include "ctc_loss_host.inl"

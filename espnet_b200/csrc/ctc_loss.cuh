@@ -3,15 +3,19 @@
 // Replaces espnet2/asr/ctc.py:46-52 (CTC.loss_fn: log_softmax + torch.nn.CTCLoss + /B)
 // and its autograd backward.  Three kernels, all in log2 units:
 //
-//   rowstats  (stream)  one warp per (utterance, frame) row: the row is staged in shared
-//                       memory by a 1-D bulk (TMA) copy, reduced to its log-sum-exp, and the
-//                       blank + label columns are gathered into lpg[b][t][0..L].
-//   sweep     (latency) one CTA per (utterance, direction): the alpha (or, on the reversed
-//                       sequence, beta) recursion over lpg, one thread per label position,
-//                       re-centred every frame so that values stay O(10) in fp32.
-//   grad      (stream)  one warp per row again: occupancies from alpha+beta, normalised per
-//                       row, softmax recomputed from the staged row, result written in place
-//                       in shared memory and bulk-stored to the gradient.
+// Fused forward+backward (b200_ctc_loss_fwd_bwd), all in log2 units:
+//   stream    (HBM)     ctc_loss_stream.inl: the one pass over the logits.  Rows are staged in a
+//                       shared-memory ring by 1-D bulk (TMA) copies; per row: log-sum-exp, the
+//                       blank + label columns gathered into lpg[b][t][0..L], and w * softmax
+//                       written in place and bulk-stored to the gradient.
+//   sweep     (latency) ctc_loss_sweep.inl: one CTA per (utterance, direction), the alpha (or, on
+//                       the reversed sequence, beta) recursion over lpg, one thread per label
+//                       position, warps skewed against each other instead of barriers,
+//                       re-centred so that values stay O(10) in fp32.
+//   patch     (L2)      ctc_loss_occ.inl<PATCH>: occupancies from alpha+beta, normalised per row,
+//                       written over the blank / label columns of the gradient.
+// Separate forward / backward calls (autograd with an upstream gradient known only later):
+//   rowstats -> sweep -> occ (forward), grad (backward, re-reads the logits) in ctc_loss_rows.inl.
 #pragma once
 #include "common.cuh"
 
@@ -19,6 +23,10 @@ namespace b200 {
 
 // marks a merged duplicate label in LossWs::occ (softmax - occupancy lies in [-1, 1])
 constexpr float kCorrSkip = 2.0f;
+// LossWs::dupcode[k]: (index of the next position with the same label) + 1 in the low bits, 0 if none;
+// kDupLater set if an earlier position carries the same label.  0 for a label that occurs once.
+constexpr int kDupLater = 0x40000000;
+constexpr int kDupNextMask = 0x3fffffff;
 
 struct LossWs {
   float* lse2;      // [B][T]      row log2-sum-exp (log2 units)
@@ -29,6 +37,7 @@ struct LossWs {
   int* labels;      // [B][Kp]     labels as int32
   int* dup_next;    // [B][Kp]     next position with the same label, or -1
   int* is_first;    // [B][Kp]     1 if no earlier position has the same label
+  int* dupcode;     // [B][Kp]     both of the above packed (see kDupLater)
   float* logz_beta; // [B]         log2 p(y|x) from the beta sweep (consistency check)
   float* nll_ws;    // [B]         copy of nll (nats) kept for the backward pass
   int* bad;         // [64]        [0] set when a label is outside [0,V) or equals blank;
@@ -55,6 +64,7 @@ inline LossWs carve_loss_ws(void* base, int64_t T, int64_t B, int64_t V, int64_t
   w.labels = (int*)take(sizeof(int) * B * w.Kp);
   w.dup_next = (int*)take(sizeof(int) * B * w.Kp);
   w.is_first = (int*)take(sizeof(int) * B * w.Kp);
+  w.dupcode = (int*)take(sizeof(int) * B * w.Kp);
   w.logz_beta = (float*)take(sizeof(float) * B);
   w.nll_ws = (float*)take(sizeof(float) * B);
   w.bad = (int*)take(sizeof(int) * 64);

@@ -118,42 +118,63 @@ static LossParams make_params(const void* logits, int64_t T, int64_t B, int64_t 
   return p;
 }
 
+static int launch_prep(const LossParams& p, cudaStream_t st);
+
 static int run_forward(LossParams p, int dtype, float* loss_sum, cudaStream_t st) {
   const int es = elem_size(dtype);
   RowsCfg cfg;
   int rc = plan_rows(p, false, rows_vec_ok(p.logits, p.V, p.stride_t, p.stride_b, es), &cfg);
   if (rc) return rc;
   B200_CUDA(cudaMemsetAsync(p.ws.bad, 0, 64 * sizeof(int), st));
-  {
-    int threads = (int)align_up((size_t)(p.Lmax > 0 ? p.Lmax : 1), 32);
-    if (threads > 1024) threads = 1024;
-    const size_t sm = sizeof(int) * (size_t)(p.Lmax > 0 ? p.Lmax : 1);
-    ctc_prep_kernel<<<(unsigned)(p.b1 - p.b0), threads, sm, st>>>(p);
-    B200_CUDA(cudaGetLastError());
-  }
+  rc = launch_prep(p, st);
+  if (rc) return rc;
   rc = launch_rows<false>(p, dtype, cfg, st);
   if (rc) return rc;
   rc = launch_sweep(p, st);
   if (rc) return rc;
-  {
-    // occupancies for the backward pass (cheap, and keeps _backward a pure stream)
-    const size_t per_warp = 2 * p.ws.Kp * sizeof(int) + p.ws.Sp * sizeof(float);
-    int warps = (int)(kRowsSmemBudget / per_warp);
-    if (warps > kRowsMaxWarps) warps = kRowsMaxWarps;
-    if (warps < 1) {
-      set_error("Lmax=%lld needs %zu bytes of shared memory per warp", (long long)p.Lmax, per_warp);
-      return B200_ERR_UNSUPPORTED_SHAPE;
-    }
-    const int smem = (int)(per_warp * warps);
-    if (smem > 48 * 1024)
-      B200_CUDA(cudaFuncSetAttribute(ctc_gamma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    ctc_gamma_kernel<<<cfg.grid, warps * 32, smem, st>>>(p);
-    B200_CUDA(cudaGetLastError());
-  }
+  // occupancies for the backward pass (cheap, and keeps _backward a pure stream)
+  rc = launch_occ(p, st);
+  if (rc) return rc;
   if (loss_sum) {
     ctc_loss_sum_kernel<<<1, 32, 0, st>>>(p.nll, (int)p.B, loss_sum);
     B200_CUDA(cudaGetLastError());
   }
+  return B200_OK;
+}
+
+static int launch_prep(const LossParams& p, cudaStream_t st) {
+  int threads = (int)align_up((size_t)(p.Lmax > 0 ? p.Lmax : 1), 32);
+  if (threads > 1024) threads = 1024;
+  const size_t sm = sizeof(int) * (size_t)(p.Lmax > 0 ? p.Lmax : 1);
+  ctc_prep_kernel<<<(unsigned)(p.b1 - p.b0), threads, sm, st>>>(p);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+// One pass over the logits (stream), the two lattice sweeps, and the column patch.
+// Returns false in *done when the shape needs the general three-pass path.
+static int run_fused(LossParams p, int dtype, float* loss_sum, cudaStream_t st, bool* done) {
+  *done = false;
+  const int es = elem_size(dtype);
+  StreamCfg sc;
+  if (p.debug & 1) return B200_OK;
+  if (!rows_vec_ok(p.logits, p.V, p.stride_t, p.stride_b, es) ||
+      !rows_vec_ok(p.grad, p.V, p.gstride_t, p.gstride_b, es) || !plan_stream(p, es, &sc))
+    return B200_OK;
+  B200_CUDA(cudaMemsetAsync(p.ws.bad, 0, 64 * sizeof(int), st));
+  int rc = launch_prep(p, st);
+  if (rc) return rc;
+  rc = launch_stream(p, dtype, sc, st);
+  if (rc) return rc;
+  rc = launch_sweep(p, st);
+  if (rc) return rc;
+  rc = launch_patch(p, dtype, st);
+  if (rc) return rc;
+  if (loss_sum) {
+    ctc_loss_sum_kernel<<<1, 32, 0, st>>>(p.nll, (int)p.B, loss_sum);
+    B200_CUDA(cudaGetLastError());
+  }
+  *done = true;
   return B200_OK;
 }
 
@@ -216,8 +237,25 @@ extern "C" int b200_ctc_loss_fwd_bwd(const void* logits, int dtype, int64_t T, i
                                      int64_t Lmax, int blank, const float* grad_weight, float grad_scale,
                                      float* nll, float* loss_sum, void* grad_logits, int64_t gstride_t,
                                      int64_t gstride_b, void* workspace, size_t workspace_bytes, void* stream) {
-  int rc = b200_ctc_loss_forward(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen,
-                                 Lmax, blank, nll, loss_sum, workspace, workspace_bytes, stream);
+  int rc = check_common(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
+                        blank, workspace, workspace_bytes);
+  if (rc) return rc;
+  B200_CHECK_ARG(nll != nullptr, B200_ERR_INVALID_ARGUMENT, "nll is null");
+  B200_CHECK_ARG(grad_logits != nullptr, B200_ERR_INVALID_ARGUMENT, "grad_logits is null");
+  B200_CHECK_ARG(gstride_t >= V || T == 1, B200_ERR_INVALID_ARGUMENT, "gradient rows overlap (gstride_t < V)");
+  {
+    LossParams p = make_params(logits, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
+                               blank, nll, workspace);
+    p.grad = grad_logits;
+    p.gstride_t = gstride_t; p.gstride_b = gstride_b;
+    p.grad_weight = grad_weight; p.grad_scale = grad_scale;
+    bool done = false;
+    rc = run_fused(p, dtype, loss_sum, (cudaStream_t)stream, &done);
+    if (rc || done) return rc;
+  }
+  // general shapes: three passes (rowstats, lattice, gradient)
+  rc = b200_ctc_loss_forward(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen,
+                             Lmax, blank, nll, loss_sum, workspace, workspace_bytes, stream);
   if (rc) return rc;
   return b200_ctc_loss_backward(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen,
                                 Lmax, blank, grad_weight, grad_scale, grad_logits, gstride_t, gstride_b,

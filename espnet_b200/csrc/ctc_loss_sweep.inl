@@ -1,37 +1,42 @@
 // ctc_loss_sweep.inl -- the alpha / beta lattice recursion (included by ctc_loss.cu).
 //
-// One CTA per utterance runs BOTH sweeps: thread i owns the logical states 2i (blank) and
-// 2i+1 (label i) of the alpha recursion and, independently, of the beta recursion, which is
-// the same recursion on the time- and label-reversed utterance (its states are stored in that
-// reversed order).  The two dependency chains interleave in the same warps, so the second
-// sweep rides in the issue slots the first one leaves empty.
+// One CTA per (utterance, direction).  Thread i owns the logical states 2i (blank) and 2i+1
+// (label i); the beta sweep is the same recursion on the time- and label-reversed utterance
+// (its states are stored in that reversed order).  The recursion only flows from low to high
+// states, so the warps of a CTA run SKEWED by one chunk of CHF frames instead of in lock step:
+// warp w starts chunk c when warp w-1 has published the label state of its last lane for the
+// frames of that chunk (a ring of floats in shared memory plus one progress word per warp).
+// There is no barrier and no branch inside a full chunk: the CHF boundary values and the CHF
+// log-prob pairs of the chunk are in registers before its first frame, and the per-frame
+// critical path is shfl.up -> ex2 -> lg2 -> add inside a warp.
 //
-// Per frame and chain the critical path is: shfl.up of the neighbour's label state (one shared
-// memory word per warp boundary) -> ex2 -> lg2 -> add -> store of the warp boundary ->
-// bar.sync.  Everything else is off that path:
-//  * the label-gathered log-prob rows lpg[b][t][0..L] are staged in shared memory kSweepRing
-//    chunks of CHF frames ahead by 1-D bulk copies (cp.async.bulk -> UBLKCP) signalling an
-//    mbarrier, so the loop never waits on global memory;
-//  * every frame subtracts an integer drift estimate, and once per chunk the measured maximum
-//    over all states (REDUX.MAX) is removed, so values stay O(10..50) in log2 units and fp32
-//    keeps ~4e-6 absolute resolution for any T; the integers are summed exactly and only enter
-//    log p(y|x) at the end (the occupancy kernel normalises per frame and never needs them).
+//  * the label-gathered log-prob rows lpg[b][t][0..L] are read straight into registers three
+//    chunks ahead (each lane needs only its own column and the blank column);
+//  * every frame subtracts an integer drift estimate and every chunk an integer correction,
+//    both derived from the maximum over all states that every warp publishes per chunk (read
+//    `delay` chunks later, when even the most skewed warp has published it), so values stay
+//    O(10) in log2 units and fp32 keeps ~4e-6 absolute resolution for any T; all warps derive
+//    the same integers from the same published data, their exact sum only enters log p(y|x)
+//    at the end (the occupancy kernels normalise per frame and never need it).
 namespace b200 {
 
-constexpr int kSweepRing = 4;
-
-struct SweepChain {
-  float ab, al;        // blank / label state of this thread
-  float dstep;         // integer drift removed every frame
-  float level_prev, corr_prev;
-  int csum;            // exact sum of everything removed so far
-  float skipmask;      // 0 if the s-2 transition is allowed, -1e30 otherwise
-  float* outp;         // where this thread's float2 of the current frame goes
-  int64_t ostep;       // +-Sp
-  int kcol;            // column of this thread's label in an lpg row
+// A value and the index of the frame (or chunk) it belongs to, written and read as ONE 8-byte
+// shared-memory access: a record validates itself, so the hand-off needs no fence (a fence would
+// also wait for the lattice stores to global memory that are in flight).
+struct __align__(8) Tagged {
+  float v;
+  int tag;
 };
+__device__ __forceinline__ Tagged lds_tagged(const Tagged* p) {
+  Tagged r;
+  asm volatile("ld.volatile.shared.v2.b32 {%0,%1}, [%2];" : "=f"(r.v), "=r"(r.tag) : "r"(smem_u32(p)));
+  return r;
+}
+__device__ __forceinline__ void sts_tagged(Tagged* p, float v, int tag) {
+  asm volatile("st.volatile.shared.v2.b32 [%0], {%1,%2};" ::"r"(smem_u32(p)), "f"(v), "r"(tag) : "memory");
+}
 
-// log2(2^hi * (1 + e0) + 2^c) where e0 = 2^(lo - hi) was computed off the critical path
+// log2(2^hi * s1 + 2^c) where s1 = 1 + 2^(lo - hi) was computed off the critical path
 __device__ __forceinline__ float lse3_pre(float hi, float s1, float c) {
   const float t = ex2f(-fabsf(c - hi));
   const float sum = (c <= hi) ? (s1 + t) : fmaf(s1, t, 1.0f);
@@ -40,223 +45,242 @@ __device__ __forceinline__ float lse3_pre(float hi, float s1, float c) {
 __device__ __forceinline__ float lse2_abs(float a, float b) {
   return fmaxf(a, b) + lg2f(1.0f + ex2f(-fabsf(a - b)));
 }
+__device__ __forceinline__ float clamp_int_f(float x) {  // integer-valued, safely inside int32/fp32-exact range
+  return fminf(fmaxf(rintf(x), -4194304.0f), 4194304.0f);
+}
+
+template <int MAXT> struct SweepRings {
+  // hand-off ring in frames: > (maximum skew = delay <= MAXT/32 chunks) + 2 chunks; level ring in
+  // chunks: > 2 * delay + 2.  Powers of two so that the ring indices are masks.
+  static constexpr int kCHF = MAXT <= 256 ? 8 : 4;
+  static constexpr int kR = MAXT <= 256 ? 128 : 256;
+  static constexpr int kWR = MAXT <= 256 ? 32 : 128;
+  static_assert(kR >= kCHF * (MAXT / 32 + 3) && kWR >= 2 * (MAXT / 32) + 4, "ring sizes");
+};
 
 template <int CHF, int MAXT>
 __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
-  extern __shared__ __align__(128) unsigned char sw_smem[];
+  extern __shared__ __align__(16) unsigned char sw_smem[];
+  constexpr int kR = SweepRings<MAXT>::kR, kWR = SweepRings<MAXT>::kWR;
+  static_assert(CHF == SweepRings<MAXT>::kCHF, "chunk size");
   const int b = p.b0 + blockIdx.x;
-  const int Tb = (int)p.ilen[b];
+  const int d = blockIdx.y;
+  const int Tb = min((int)p.ilen[b], (int)p.T);
   const int L = (int)p.olen[b];
   const int i = threadIdx.x;
   const int lane = i & 31, warp = i >> 5;
   const int nw = blockDim.x >> 5;
-  const int64_t Kp = p.ws.Kp, Sp = p.ws.Sp;
-
-  __shared__ float s_bnd[2][2][36];   // [dir][frame parity][warp]; slot 32 holds log(0) for warp 0
-  __shared__ float s_wmax[2][2][32];  // [dir][chunk parity][warp]
-  __shared__ float s_fin[2][2];
-  uint64_t* full = reinterpret_cast<uint64_t*>(sw_smem);  // [2][kSweepRing]
-  float* ring = reinterpret_cast<float*>(sw_smem + 128);  // [2][kSweepRing][CHF*Kp]
-  const int chunk_floats = CHF * (int)Kp;
+  const int Kp = (int)p.ws.Kp;
+  const int64_t Sp = p.ws.Sp;
+  const int nwa = L / 32 + 1;  // warps that own at least one state (threads 0..L)
+  Tagged* s_bnd = reinterpret_cast<Tagged*>(sw_smem);  // [nw][kR] label state of lane 31 of warp w at frame f
+  Tagged* s_wmx = s_bnd + (size_t)nw * kR;             // [kWR][nw] maximum over the states of warp w at the start of chunk c
+  int* s_hist = reinterpret_cast<int*>(s_wmx + (size_t)kWR * nw);  // [kWR] total removed before chunk c
+  __shared__ float s_fin[2];
 
   if (Tb <= 0) {
     if (i == 0) {
-      p.nll[b] = p.ws.nll_ws[b] = (L == 0) ? 0.0f : __int_as_float(0x7f800000);
-      p.ws.logz_beta[b] = (L == 0) ? 0.0f : B200_NEG;
+      if (d == 0) p.nll[b] = p.ws.nll_ws[b] = (L == 0) ? 0.0f : __int_as_float(0x7f800000);
+      else p.ws.logz_beta[b] = (L == 0) ? 0.0f : B200_NEG;
     }
     return;
   }
-  for (int k = i; k < 2 * 2 * 36; k += blockDim.x) (&s_bnd[0][0][0])[k] = B200_NEG;
-  for (int k = i; k < 2 * 2 * 32; k += blockDim.x) (&s_wmax[0][0][0])[k] = B200_NEG;
-  if (i == 0) {
-    for (int s = 0; s < 2 * kSweepRing; ++s) mbar_init(&full[s], 1);
-    mbar_fence_init();
-  }
+  for (int k = i; k < nw * kR + kWR * nw; k += blockDim.x) s_bnd[k].tag = -1;
   __syncthreads();
-
-  const float* lpg = p.ws.lpg + (int64_t)b * p.T * Kp;
-  const int nchunks = (Tb + CHF - 1) / CHF;
-  auto issue_chunk = [&](int c) {  // thread 0 only: chunk c of both directions
-    const int f0 = c * CHF;
-    const int n = min(CHF, Tb - f0);
-    const int slot = c % kSweepRing;
-    const uint32_t bytes = (uint32_t)(n * Kp * sizeof(float));
-#pragma unroll
-    for (int d = 0; d < 2; ++d) {
-      const int phys0 = d ? (Tb - f0 - n) : f0;
-      uint64_t* bar = &full[d * kSweepRing + slot];
-      mbar_arrive_expect_tx(bar, bytes);
-      bulk_g2s(ring + ((size_t)d * kSweepRing + slot) * chunk_floats, lpg + (int64_t)phys0 * Kp, bytes, bar);
-    }
-  };
-  if (i == 0)
-    for (int c = 0; c < kSweepRing - 1 && c < nchunks; ++c) issue_chunk(c);
+  if (warp >= nwa) return;
 
   const int* lab = p.ws.labels + (int64_t)b * Kp;
   const bool has_label = i < L;
   const bool active = i <= L;
-  SweepChain ch[2];
-#pragma unroll
-  for (int d = 0; d < 2; ++d) {
-    const int pi = d ? (L - 1 - i) : i;  // physical label position of logical position i
-    bool skip_ok = false;
-    if (has_label && i >= 1) skip_ok = lab[pi] != lab[d ? pi + 1 : pi - 1];
-    ch[d].skipmask = skip_ok ? 0.0f : B200_NEG;
-    ch[d].kcol = has_label ? 1 + pi : 0;
-    ch[d].ab = B200_NEG; ch[d].al = B200_NEG;
-    ch[d].dstep = 0.f; ch[d].level_prev = 0.f; ch[d].corr_prev = 0.f; ch[d].csum = 0;
-    ch[d].outp = p.ws.lat + (((int64_t)d * p.B + b) * p.T + (d ? (Tb - 1) : 0)) * Sp + 2 * i;
-    ch[d].ostep = d ? -Sp : Sp;
-  }
-  const int bsrc = warp ? warp - 1 : 32;
+  const int pi = d ? (L - 1 - i) : i;  // physical label position of logical position i
+  bool skip_ok = false;
+  if (has_label && i >= 1) skip_ok = lab[pi] != lab[d ? pi + 1 : pi - 1];
+  const float skipmask = skip_ok ? 0.0f : B200_NEG;
+  const int kcol = has_label ? 1 + pi : 0;
+  // logical frame f is physical frame f (alpha) or Tb-1-f (beta): rows of lpg and of the lattice
+  const float* lp0 = p.ws.lpg + ((int64_t)b * p.T + (d ? (Tb - 1) : 0)) * Kp;
+  const int lstep = d ? -Kp : Kp;
+  float* outp = p.ws.lat + (((int64_t)d * p.B + b) * p.T + (d ? (Tb - 1) : 0)) * Sp + 2 * i;
+  const int64_t ostep = d ? -Sp : Sp;
   const bool lane0 = lane == 0, lane31 = lane == 31;
+  const bool poll = warp > 0;
+  const Tagged* bsrc = s_bnd + (size_t)(poll ? warp - 1 : 0) * kR;
+  Tagged* bdst = s_bnd + (size_t)warp * kR;
+  // the most skewed warp publishes its level of chunk m when warp 0 is around chunk m + nwa - 1
+  const int delay = nwa;
 
-  for (int c = 0; c < nchunks; ++c) {
-    const int slot = c % kSweepRing;
+  float ab = B200_NEG, al = B200_NEG;
+  float dstep = 0.f;
+  int csum = 0;                      // exact sum of everything removed so far
+  float xprev = 0.f; int sprev = 0;  // previous consumed level measurement and its csum
+  bool have_prev = false;
+
+  // one frame of the recursion; bn = label state of the last lane of the previous warp at the previous frame
+  auto frame = [&](float lb_t, float ll_t, float bn, float o, int fr) {
+    const float sh = __shfl_up_sync(0xffffffffu, al, 1);
+    const float nbr = lane0 ? bn : sh;
+    const float hi = fmaxf(al, ab);
+    const float s1 = 1.0f + ex2f(-fabsf(al - ab));
+    const float x = lse2_abs(ab, nbr);
+    const float y = lse3_pre(hi, s1, nbr + skipmask);
+    ab = (lb_t - o) + x;
+    al = (ll_t - o) + y;
+    if (lane31) sts_tagged(&bdst[fr & (kR - 1)], al, fr);
+    if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
+    outp += ostep;
+  };
+  // start of chunk c >= 1 (n frames): publish this warp's level, consume everybody's of chunk
+  // c - delay, derive the integer removals of this chunk (dstep per frame, corr once)
+  auto chunk_begin = [&](int c, int n) -> float {
+    float corr = 0.f;
+    const float wm = warp_max_redux(fmaxf(ab, al));
+    if (lane31) {
+      sts_tagged(&s_wmx[(c & (kWR - 1)) * nw + warp], wm, c);
+      s_hist[c & (kWR - 1)] = csum;
+    }
+    __syncwarp();
+    const int cm = c - delay;
+    if (cm >= 1) {
+      Tagged e;
+      e.v = B200_NEG; e.tag = cm;
+      if (lane < nwa) {
+        const Tagged* src = &s_wmx[(cm & (kWR - 1)) * nw + lane];
+        do { e = lds_tagged(src); } while (e.tag != cm);
+      }
+      __syncwarp();
+      const float xm = warp_max_redux(e.v);
+      const int sm = s_hist[cm & (kWR - 1)];
+      // uncentred level y = x + S; drift per frame from two consecutive measurements
+      float delta = dstep;
+      if (have_prev) delta = (xm - xprev + (float)(sm - sprev)) * (1.0f / CHF);
+      xprev = xm; sprev = sm; have_prev = true;
+      const float xhat = xm + (float)(sm - csum) + delta * (float)(CHF * delay);  // level now
+      dstep = clamp_int_f(delta);
+      corr = clamp_int_f(clamp_int_f(xhat + delta * (float)n) - dstep * (float)n);
+    }
+    return corr;
+  };
+  // generic (slow) chunk: the first chunk and a trailing partial chunk; reads lpg directly
+  auto slow_chunk = [&](int c, int n) {
     const int f0 = c * CHF;
-    const int n = min(CHF, Tb - f0);
-    // fill the slot freed by the previous chunk (its last frame ended with a barrier)
-    if (i == 0 && c + kSweepRing - 1 < nchunks) issue_chunk(c + kSweepRing - 1);
-    float vb[2][CHF], vl[2][CHF];
-#pragma unroll
-    for (int d = 0; d < 2; ++d) {
-      mbar_wait(&full[d * kSweepRing + slot], (uint32_t)((c / kSweepRing) & 1));
-      const float* buf = ring + ((size_t)d * kSweepRing + slot) * chunk_floats;
-#pragma unroll
-      for (int f = 0; f < CHF; ++f) {
-        if (f < n) {
-          const float* rowp = buf + (size_t)(d ? (n - 1 - f) : f) * Kp;
-          vb[d][f] = rowp[0];
-          vl[d][f] = has_label ? rowp[ch[d].kcol] : B200_NEG;  // a missing label state stays at log(0)
-        } else {
-          vb[d][f] = 0.f; vl[d][f] = 0.f;
-        }
-      }
-    }
+    float corr = 0.f;
     if (c == 0) {
-#pragma unroll
-      for (int d = 0; d < 2; ++d) {
-        // frame 0: only the first blank and the first label are reachable
-        if (i == 0) { ch[d].ab = vb[d][0]; ch[d].al = vl[d][0]; }
-        if (active) *reinterpret_cast<float2*>(ch[d].outp) = make_float2(ch[d].ab, ch[d].al);
-        ch[d].outp += ch[d].ostep;
-        if (lane31) s_bnd[d][0][warp] = ch[d].al;
-        if (n > 1) ch[d].dstep = floorf(vb[d][1]);
-      }
+      if (Tb > 1) dstep = clamp_int_f(floorf(ld_nc_f32(lp0 + lstep)));
+      if (lane31) s_hist[0] = 0;
     } else {
-#pragma unroll
-      for (int d = 0; d < 2; ++d) {
-        const float wm = warp_max_redux(fmaxf(ch[d].ab, ch[d].al));
-        if (lane0) s_wmax[d][c & 1][warp] = wm;
+      corr = chunk_begin(c, n);
+    }
+    for (int f = 0; f < n; ++f) {
+      const int fr = f0 + f;
+      const float* rowp = lp0 + (int64_t)fr * lstep;
+      const float lb_t = ld_nc_f32(rowp);
+      const float ll_t = has_label ? ld_nc_f32(rowp + kcol) : B200_NEG;
+      if (fr == 0) {
+        // frame 0: only the first blank and the first label are reachable
+        if (i == 0) { ab = lb_t; al = ll_t; }
+        if (lane31) sts_tagged(&bdst[0], al, 0);
+        if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
+        outp += ostep;
+      } else {
+        Tagged e;
+        e.v = B200_NEG; e.tag = fr - 1;
+        if (poll) {
+          do { e = lds_tagged(&bsrc[(fr - 1) & (kR - 1)]); } while (e.tag != fr - 1);
+        }
+        frame(lb_t, ll_t, e.v, dstep + (f == 0 ? corr : 0.f), fr);
       }
     }
-    if (nw > 1) __syncthreads(); else __syncwarp();
-    float corr[2] = {0.f, 0.f};
-    if (c > 0) {
-#pragma unroll
-      for (int d = 0; d < 2; ++d) {
-        const float level = warp_max_redux(s_wmax[d][c & 1][lane]);
-        corr[d] = floorf(level);
-        // drift per frame seen over the last chunk, relative to the dstep that was applied
-        ch[d].dstep = floorf(ch[d].dstep + (level - ch[d].level_prev + ch[d].corr_prev) * (1.0f / CHF) + 0.5f);
-        ch[d].level_prev = level;
-        ch[d].corr_prev = corr[d];
-      }
-    }
+    csum += (n - (c == 0 ? 1 : 0)) * (int)dstep + (int)corr;
+  };
+  // registers of one full chunk, loaded three chunks ahead of their use
+  auto load_chunk = [&](int c, float(&xb)[CHF], float(&xl)[CHF]) {
+    const float* rowp = lp0 + (int64_t)(c * CHF) * lstep;
 #pragma unroll
     for (int f = 0; f < CHF; ++f) {
-      if (f < n && !(c == 0 && f == 0)) {
-        const int par = (CHF & 1) ? ((f0 + f) & 1) : (f & 1);
-        // neighbour's label state of the previous frame: lane-1 by shuffle, across the warp
-        // boundary through one shared-memory word (loaded by every lane, in parallel with the shuffle)
-        float nbr[2];
-#pragma unroll
-        for (int d = 0; d < 2; ++d) {
-          const float bn = s_bnd[d][par ^ 1][bsrc];
-          const float sh = __shfl_up_sync(0xffffffffu, ch[d].al, 1);
-          nbr[d] = lane0 ? bn : sh;
-        }
-#pragma unroll
-        for (int d = 0; d < 2; ++d) {
-          SweepChain& s = ch[d];
-          const float o = s.dstep + ((f == 0) ? corr[d] : 0.f);
-          const float hi = fmaxf(s.al, s.ab);
-          const float s1 = 1.0f + ex2f(-fabsf(s.al - s.ab));
-          const float lb = vb[d][f] - o, ll = vl[d][f] - o;
-          const float x = lse2_abs(s.ab, nbr[d]);
-          const float y = lse3_pre(hi, s1, nbr[d] + s.skipmask);
-          s.ab = lb + x;
-          s.al = ll + y;
-          if (lane31) s_bnd[d][par][warp] = s.al;
-          if (active) *reinterpret_cast<float2*>(s.outp) = make_float2(s.ab, s.al);
-          s.outp += s.ostep;
-        }
-        if (nw > 1) __syncthreads(); else __syncwarp();
-      }
+      xb[f] = ld_nc_f32(rowp);
+      xl[f] = has_label ? ld_nc_f32(rowp + kcol) : B200_NEG;  // a missing label state stays at log(0)
+      rowp += lstep;
     }
-    // exact bookkeeping of what this chunk removed (frame 0 of the utterance removes nothing)
+  };
+  // full chunk c >= 1: straight-line code, no branch inside the frames
+  auto fast_chunk = [&](int c, const float(&xb)[CHF], const float(&xl)[CHF]) {
+    const int f0 = c * CHF;
+    const float corr = chunk_begin(c, CHF);
+    float bn[CHF];
 #pragma unroll
-    for (int d = 0; d < 2; ++d) ch[d].csum += (n - (c == 0 ? 1 : 0)) * (int)ch[d].dstep + (int)corr[d];
-  }
+    for (int f = 0; f < CHF; ++f) bn[f] = B200_NEG;
+    if (poll) {
+      // boundary values of frames f0-1 .. f0+CHF-2 from the previous warp
+      bool ok;
+      do {
+        ok = true;
+#pragma unroll
+        for (int f = 0; f < CHF; ++f) {
+          const Tagged e = lds_tagged(&bsrc[(f0 + f - 1) & (kR - 1)]);
+          bn[f] = e.v;
+          ok = ok && (e.tag == f0 + f - 1);
+        }
+      } while (!ok);
+    }
+#pragma unroll
+    for (int f = 0; f < CHF; ++f) frame(xb[f], xl[f], bn[f], dstep + (f == 0 ? corr : 0.f), f0 + f);
+    csum += CHF * (int)dstep + (int)corr;
+  };
 
-  // log2 p(y|x) = lse2(state 2L, state 2L-1) + sum of offsets, from both sweeps
-#pragma unroll
-  for (int d = 0; d < 2; ++d) {
-    if (i == L) s_fin[d][0] = ch[d].ab;
-    if (L == 0 && i == 0) s_fin[d][1] = B200_NEG;
-    if (L > 0 && i == L - 1) s_fin[d][1] = ch[d].al;
+  const int nfull = Tb / CHF;  // chunks 1 .. nfull-1 are full and take the fast path
+  float rb0[CHF], rl0[CHF], rb1[CHF], rl1[CHF], rb2[CHF], rl2[CHF];
+  if (1 < nfull) load_chunk(1, rb0, rl0);
+  if (2 < nfull) load_chunk(2, rb1, rl1);
+  if (3 < nfull) load_chunk(3, rb2, rl2);
+  slow_chunk(0, min(CHF, Tb));
+  int c = 1;
+  while (c < nfull) {
+    fast_chunk(c, rb0, rl0);
+    if (c + 3 < nfull) load_chunk(c + 3, rb0, rl0);
+    if (++c >= nfull) break;
+    fast_chunk(c, rb1, rl1);
+    if (c + 3 < nfull) load_chunk(c + 3, rb1, rl1);
+    if (++c >= nfull) break;
+    fast_chunk(c, rb2, rl2);
+    if (c + 3 < nfull) load_chunk(c + 3, rb2, rl2);
+    ++c;
   }
-  __syncthreads();
+  if (nfull >= 1 && Tb > nfull * CHF) slow_chunk(nfull, Tb - nfull * CHF);
+
+  // log2 p(y|x) = lse2(state 2L, state 2L-1) + sum of offsets
+  if (i == L) s_fin[0] = ab;
+  if (L == 0 && i == 0) s_fin[1] = B200_NEG;
+  if (L > 0 && i == L - 1) s_fin[1] = al;
+  asm volatile("bar.sync 1, %0;" ::"r"(nwa * 32) : "memory");
   if (i == 0) {
-#pragma unroll
-    for (int d = 0; d < 2; ++d) {
-      const float z = lse2(s_fin[d][0], s_fin[d][1]);
-      const bool feasible = z > -1.0e29f;
-      const float logz2 = z + (float)ch[d].csum;
-      if (d == 0) p.nll[b] = p.ws.nll_ws[b] = feasible ? -B200_LN2 * logz2 : __int_as_float(0x7f800000);
-      else p.ws.logz_beta[b] = feasible ? logz2 : B200_NEG;
-    }
+    const float z = lse2(s_fin[0], s_fin[1]);
+    const bool feasible = z > -1.0e29f;
+    const float logz2 = z + (float)csum;
+    if (d == 0) p.nll[b] = p.ws.nll_ws[b] = feasible ? -B200_LN2 * logz2 : __int_as_float(0x7f800000);
+    else p.ws.logz_beta[b] = feasible ? logz2 : B200_NEG;
   }
 }
 
-struct SweepCfg {
-  int threads, chf, smem;
-};
-
-inline SweepCfg plan_sweep(const LossParams& p) {
-  SweepCfg c;
-  c.threads = (int)align_up((size_t)(p.Lmax + 1), 32);
-  int chf = (int)(8192 / (p.ws.Kp * sizeof(float)));
-  c.chf = chf >= 8 ? 8 : (chf >= 4 ? 4 : (chf >= 2 ? 2 : 1));
-  c.smem = 128 + 2 * kSweepRing * c.chf * (int)p.ws.Kp * (int)sizeof(float);
-  return c;
+template <int MAXT>
+static size_t sweep_smem_bytes(int nw) {
+  const size_t kR = SweepRings<MAXT>::kR, kWR = SweepRings<MAXT>::kWR;
+  return sizeof(Tagged) * nw * kR + sizeof(Tagged) * kWR * nw + sizeof(int) * kWR;
 }
 
 template <int CHF, int MAXT>
-static int launch_sweep_t(const LossParams& p, const SweepCfg& c, cudaStream_t st) {
+static int launch_sweep_t(const LossParams& p, int threads, cudaStream_t st) {
+  const size_t smem = sweep_smem_bytes<MAXT>(threads / 32);
   auto kern = ctc_sweep_kernel<CHF, MAXT>;
-  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem));
-  kern<<<(unsigned)(p.b1 - p.b0), c.threads, c.smem, st>>>(p);
+  if (smem > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<dim3((unsigned)(p.b1 - p.b0), 2), threads, smem, st>>>(p);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }
 
 static int launch_sweep(const LossParams& p, cudaStream_t st) {
-  const SweepCfg c = plan_sweep(p);
-  if (c.threads <= 256) {
-    switch (c.chf) {
-      case 8: return launch_sweep_t<8, 256>(p, c, st);
-      case 4: return launch_sweep_t<4, 256>(p, c, st);
-      case 2: return launch_sweep_t<2, 256>(p, c, st);
-      default: return launch_sweep_t<1, 256>(p, c, st);
-    }
-  }
-  switch (c.chf) {
-    case 8: return launch_sweep_t<8, 1024>(p, c, st);
-    case 4: return launch_sweep_t<4, 1024>(p, c, st);
-    case 2: return launch_sweep_t<2, 1024>(p, c, st);
-    default: return launch_sweep_t<1, 1024>(p, c, st);
-  }
+  const int threads = (int)align_up((size_t)(p.Lmax + 1), 32);
+  if (threads <= 256) return launch_sweep_t<8, 256>(p, threads, st);
+  return launch_sweep_t<4, 1024>(p, threads, st);
 }
 
 }  // namespace b200

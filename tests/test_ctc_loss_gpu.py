@@ -20,8 +20,12 @@ TOL_F32 = 1e-5
 TOL_BF16 = 1e-2
 
 
-def _run(x_btv, ilen, olen, ys, grad_scale=None, dtype=None, strided=True):
-    """Returns (nll (B,) float64 numpy, grad (B,T,V) float64 numpy, loss_sum)."""
+def _run(x_btv, ilen, olen, ys, grad_scale=None, dtype=None, strided=True, split=False):
+    """Returns (nll (B,) float64 numpy, grad (B,T,V) float64 numpy, loss_sum).
+
+    split=False: the fused b200_ctc_loss_fwd_bwd call (one pass over the logits when the rows are
+    16-byte aligned); split=True: b200_ctc_loss_forward, then b200_ctc_loss_backward with the
+    upstream gradient, as autograd drives them."""
     from espnet_b200 import ctc_loss as CL
 
     B, T, V = x_btv.shape
@@ -29,6 +33,14 @@ def _run(x_btv, ilen, olen, ys, grad_scale=None, dtype=None, strided=True):
     xt = xd.transpose(0, 1) if strided else xd.transpose(0, 1).contiguous()
     L = ys.shape[1]
     off = torch.arange(B) * L
+    if split:
+        xt = xt.detach().requires_grad_()
+        nll = CL.ctc_nll(xt, ys.cuda().reshape(-1), off, ilen, olen, L)
+        w = torch.full((B,), 1.0 / B if grad_scale is None else grad_scale, device="cuda")
+        nll.backward(w)
+        torch.cuda.synchronize()
+        return (nll.detach().double().cpu().numpy(), xt.grad.transpose(0, 1).double().cpu().numpy(),
+                float(nll.detach().sum().item()))
     nll, ls, grad = CL.ctc_loss_fwd_bwd(xt, ys.cuda().reshape(-1), off, ilen, olen, L,
                                         grad_scale=(1.0 / B if grad_scale is None else grad_scale))
     torch.cuda.synchronize()
@@ -50,12 +62,13 @@ def _normrel(a, b):
     return np.abs(a[ok] - b[ok]).max() / max(np.abs(b[ok]).max(), 1e-30)
 
 
+@pytest.mark.parametrize("split", [False, True])
 @pytest.mark.parametrize("name", ["c1", "tiny", "v64", "repeats"])
-def test_fp32_matches_golden_reference(name):
+def test_fp32_matches_golden_reference(name, split):
     g = golden(f"loss_{name}.npz")
     x, ilen, olen, ys = (torch.from_numpy(g[k]) for k in ("x", "ilen", "olen", "ys"))
     B = x.shape[0]
-    nll, grad, ls = _run(x, ilen, olen, ys)
+    nll, grad, ls = _run(x, ilen, olen, ys, split=split)
     ref_nll = g["nll_over_B_f64"] * B
     np.testing.assert_allclose(nll, ref_nll, rtol=TOL_F32)
     np.testing.assert_allclose(ls / B, g["loss_f64"], rtol=TOL_F32)
@@ -65,13 +78,20 @@ def test_fp32_matches_golden_reference(name):
     assert _normrel(grad, g["grad_f32"].astype(np.float64)) <= max(TOL_F32, 2 * gap)
 
 
-def test_edge_cases_match_reference():
+@pytest.mark.parametrize("split,V4", [(False, False), (True, False), (False, True)])
+def test_edge_cases_match_reference(split, V4):
     """Empty target, single-frame utterance, infeasible utterances: inf loss and NaN gradient
-    exactly where torch.nn.CTCLoss(zero_infinity=False) puts them."""
+    exactly where torch.nn.CTCLoss(zero_infinity=False) puts them.  V4 pads the vocabulary with
+    three -inf columns (V=8: 16-byte rows) so that the one-pass kernels see the same problem."""
     g = golden("loss_edge.npz")
     x, ilen, olen, ys = (torch.from_numpy(g[k]) for k in ("x", "ilen", "olen", "ys"))
     B = x.shape[0]
-    nll, grad, _ = _run(x, ilen, olen, ys)
+    if V4:
+        x = torch.cat([x, torch.full(x.shape[:2] + (3,), -float("inf"))], dim=2)
+    nll, grad, _ = _run(x, ilen, olen, ys, split=split)
+    if V4:
+        assert (grad[..., 5:][~np.isnan(grad[..., 5:])] == 0).all()
+        grad = grad[..., :5]
     ref_nll = g["nll_over_B_f64"] * B
     fin = np.isfinite(ref_nll)
     assert (np.isposinf(nll) == ~fin).all() and (~fin).sum() >= 1 and fin.sum() >= 2
@@ -86,6 +106,9 @@ def test_half_precision_logits(dtype, tol):
     c = _cases.make_loss_case(6, 120, 256, 30, seed=77, dtype=dtype)
     x = c["x"]
     nll, grad, _ = _run(x, c["ilen"], c["olen"], c["ys"])
+    nll2, grad2, _ = _run(x, c["ilen"], c["olen"], c["ys"], split=True)
+    np.testing.assert_allclose(nll2, nll, rtol=1e-6)
+    assert _normrel(grad2, grad) <= tol
     rn, rg = _ref64(x.float(), c["ilen"], c["olen"], c["ys"])
     np.testing.assert_allclose(nll, rn, rtol=TOL_F32)  # fp32 accumulation: loss stays tight
     assert _normrel(grad, rg) <= tol
