@@ -34,6 +34,26 @@ int max_smem_optin(); // max dynamic shared memory per block (opt-in)
     if (e__ != cudaSuccess) return ::b200::cuda_fail(e__, #expr); \
   } while (0)
 
+// Kernel launch with (optionally) programmatic stream serialization: the kernel may be staged
+// while its predecessor in the stream is still running and synchronises with it on the device
+// (griddepcontrol.wait / flags in global memory).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                 bool pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  static const bool no_pdl = getenv("B200_NO_PDL") != nullptr;  // developer switch
+  cfg.numAttrs = (pdl && !no_pdl) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // ---------------------------------------------------------------- math
 // Everything on the lattice is kept in log2 units so that the recursion uses
 // the MUFU ex2/lg2 units directly.
@@ -220,6 +240,23 @@ __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+// programmatic dependent launch (PDL): no-ops when the kernel was launched without the attribute
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// L2-coherent loads for data another kernel of the same call is still producing
+__device__ __forceinline__ float ld_cg_f32(const float* p) {
+  float r;
+  asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ float ld_relaxed_f32(const float* p) {
+  float r;
+  asm volatile("ld.relaxed.gpu.global.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_relaxed_f32(float* p, float v) {
+  asm volatile("st.relaxed.gpu.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
 __device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
   uint4 r;
   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"

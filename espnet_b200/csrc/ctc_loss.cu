@@ -8,6 +8,7 @@ namespace b200 {
 // prep: labels -> int32, duplicate chains (deterministic, atomics-free gradient)
 // ============================================================================
 __global__ void ctc_prep_kernel(LossParams p) {
+  pdl_launch_dependents();  // the stream kernel may be staged (it waits for this grid before it reads labels)
   const int b = p.b0 + blockIdx.x;
   const int64_t L = p.olen[b];
   const int64_t* y = p.targets + p.tgt_offsets[b];
@@ -39,6 +40,29 @@ __global__ void ctc_prep_kernel(LossParams p) {
     fst[i] = first;
     nxt[i] = n;
     dc[i] = (first ? 0 : kDupLater) | (n + 1);
+  }
+  // rank of this utterance by decreasing frame count (ties by index): order[rank] = b
+  __shared__ int s_rank;
+  if (threadIdx.x == 0) s_rank = 0;
+  __syncthreads();
+  {
+    const int64_t mine = p.ilen[b];
+    int cnt = 0;
+    for (int o = p.b0 + threadIdx.x; o < p.b1; o += blockDim.x) {
+      const int64_t other = p.ilen[o];
+      cnt += (other > mine || (other == mine && o < b)) ? 1 : 0;
+    }
+    if (cnt) atomicAdd(&s_rank, cnt);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) p.ws.order[p.b0 + s_rank] = b;
+  if (p.wait_rows) {
+    // fused call: the sweeps start before the stream kernel has produced lpg; NaN = "not yet"
+    const int Tb = min((int)p.ilen[b], (int)p.T);
+    uint4* dst = reinterpret_cast<uint4*>(p.ws.lpg + (int64_t)b * p.T * p.ws.Kp);  // Kp % 8 == 0: 16-byte rows
+    const int64_t n4 = (int64_t)Tb * p.ws.Kp / 4;
+    const uint4 nanv = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+    for (int64_t k = threadIdx.x; k < n4; k += blockDim.x) dst[k] = nanv;
   }
 }
 

@@ -40,8 +40,10 @@ struct LossWs {
   int* dupcode;     // [B][Kp]     both of the above packed (see kDupLater)
   float* logz_beta; // [B]         log2 p(y|x) from the beta sweep (consistency check)
   float* nll_ws;    // [B]         copy of nll (nats) kept for the backward pass
-  int* bad;         // [64]        [0] set when a label is outside [0,V) or equals blank;
-                    //             [1], [2], [3] task counters of the rowstats / gradient / occupancy kernels
+  int* bad;         // [64 + B]    [0] set when a label is outside [0,V) or equals blank;
+                    //             [1], [2] task counters of the rowstats / gradient kernels, [4] utterances
+                    //             whose nll is final; zeroed at the start of every call
+  int* order;       // [B]         utterances by decreasing ilen (rank -> b): long lattices start first
   int64_t Kp, Sp;
   size_t bytes;
 };
@@ -68,6 +70,7 @@ inline LossWs carve_loss_ws(void* base, int64_t T, int64_t B, int64_t V, int64_t
   w.logz_beta = (float*)take(sizeof(float) * B);
   w.nll_ws = (float*)take(sizeof(float) * B);
   w.bad = (int*)take(sizeof(int) * 64);
+  w.order = (int*)take(sizeof(int) * B);
   w.bytes = off;
   return w;
 }
@@ -89,6 +92,9 @@ struct LossParams {
   float* nll;
   LossWs ws;
   int b0, b1;     // utterance range handled by this launch
+  int wait_rows;  // fused call: prep fills lpg with NaN, the sweeps run under the stream kernel and spin on
+                  // every lpg word they need until it is a number (the stream kernel never writes a NaN)
+  float* loss_sum; // sum_b nll[b], written by the sweep CTA that finishes last (may be NULL)
   int debug;      // developer experiments (B200_DEBUG_VARIANT), 0 in production
 };
 

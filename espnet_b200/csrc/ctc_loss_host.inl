@@ -130,16 +130,11 @@ static int run_forward(LossParams p, int dtype, float* loss_sum, cudaStream_t st
   if (rc) return rc;
   rc = launch_rows<false>(p, dtype, cfg, st);
   if (rc) return rc;
+  p.loss_sum = loss_sum;  // written by the sweep CTA that finishes last
   rc = launch_sweep(p, st);
   if (rc) return rc;
   // occupancies for the backward pass (cheap, and keeps _backward a pure stream)
-  rc = launch_occ(p, st);
-  if (rc) return rc;
-  if (loss_sum) {
-    ctc_loss_sum_kernel<<<1, 32, 0, st>>>(p.nll, (int)p.B, loss_sum);
-    B200_CUDA(cudaGetLastError());
-  }
-  return B200_OK;
+  return launch_occ(p, st);
 }
 
 static int launch_prep(const LossParams& p, cudaStream_t st) {
@@ -162,18 +157,22 @@ static int run_fused(LossParams p, int dtype, float* loss_sum, cudaStream_t st, 
       !rows_vec_ok(p.grad, p.V, p.gstride_t, p.gstride_b, es) || !plan_stream(p, es, &sc))
     return B200_OK;
   B200_CUDA(cudaMemsetAsync(p.ws.bad, 0, 64 * sizeof(int), st));
+  p.loss_sum = loss_sum;
+  // Running the sweeps UNDER the stream kernel (debug bit 4: prep fills lpg with NaN, the sweeps spin on
+  // the words they need) was measured slower than running them after it (325 vs 278 us at C2): the
+  // latency-bound sweep warps lose their issue slots to the 17 busy stream warps of the same SM.
+  p.wait_rows = (p.debug & 4) ? 1 : 0;
   int rc = launch_prep(p, st);
   if (rc) return rc;
+  // stream, sweeps and patch are chained by programmatic dependent launch: the sweeps run UNDER
+  // the stream kernel (each waits for the rows of its own utterance), the patch is staged under
+  // the sweeps
   rc = launch_stream(p, dtype, sc, st);
   if (rc) return rc;
-  rc = launch_sweep(p, st);
+  rc = launch_sweep(p, st, true);
   if (rc) return rc;
   rc = launch_patch(p, dtype, st);
   if (rc) return rc;
-  if (loss_sum) {
-    ctc_loss_sum_kernel<<<1, 32, 0, st>>>(p.nll, (int)p.B, loss_sum);
-    B200_CUDA(cudaGetLastError());
-  }
   *done = true;
   return B200_OK;
 }

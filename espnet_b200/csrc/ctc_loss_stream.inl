@@ -21,6 +21,7 @@
 //             leaves with one bulk shared->global copy; when that copy has read the slot, the
 //             group arrives on the slot's `empty` mbarrier and the producer refills it.
 // Bytes in flight per SM are set by the ring (~200 KB), not by registers or occupancy.
+#include <type_traits>
 namespace b200 {
 
 constexpr int kStreamWarps = 16;
@@ -90,7 +91,7 @@ __device__ __forceinline__ StreamRow stream_row(const LossParams& p, int64_t bas
   r.in_range = g < nrows;
   r.b = 0; r.t = 0; r.valid = false;
   if (r.in_range) {
-    r.b = p.b0 + (int)(g / p.T);
+    r.b = p.ws.order[p.b0 + (int)(g / p.T)];  // longest utterances first: their sweeps start first
     r.t = (int)(g % p.T);
     r.valid = r.t < (int)p.ilen[r.b];
   }
@@ -117,8 +118,7 @@ __device__ __forceinline__ void group_sync(int id, int threads) {
 }
 
 template <typename T, int G>
-__global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1)
-ctc_stream_kernel(LossParams p, int nslots, int slot_bytes) {
+__global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(LossParams p, int nslots, int slot_bytes) {
   extern __shared__ __align__(128) unsigned char st_smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(st_smem);  // [kStreamMaxSlots]
   uint64_t* empty = full + kStreamMaxSlots;               // [kStreamMaxSlots]
@@ -141,6 +141,11 @@ ctc_stream_kernel(LossParams p, int nslots, int slot_bytes) {
     mbar_fence_init();
   }
   __syncthreads();
+  // programmatic dependent launch: everything above overlapped the tail of the prep kernel; its
+  // results (labels, order) are needed from here on.  The lattice sweeps of this call may be
+  // staged from now on (they wait for this grid to finish).
+  pdl_wait();
+  pdl_launch_dependents();
 
   if (warp == kStreamWarps) {
     // ------------------------------------------------------------------ producer
@@ -183,6 +188,8 @@ ctc_stream_kernel(LossParams p, int nslots, int slot_bytes) {
   // -------------------------------------------------------------------- consumers
   const int grp = warp / G, wg = warp % G;
   const int gtid = wg * 32 + lane;
+  const int nfull = nvec / GT;
+  const bool tail = gtid + GT * nfull < nvec;
   const int bar_id = 1 + grp;
   int k = 0;
   for (int64_t base = 0;; base += 32) {
@@ -217,21 +224,30 @@ ctc_stream_kernel(LossParams p, int nslots, int slot_bytes) {
       float xg[kStreamGather];
 #pragma unroll
       for (int g = 0; g < kStreamGather; ++g) xg[g] = ElemTraits<T>::to_float(sT[col[g]]);
+      // (label positions beyond the register slots: raw value parked in the occupancy buffer, which
+      // nobody reads before the patch kernel; lpg itself only ever receives FINAL values, because the
+      // sweeps running under this kernel treat any non-NaN word of lpg as valid)
+      float* park = p.ws.occ + row * Kp;
       for (int kk = gtid + GT * kStreamGather; kk <= L; kk += GT)
-        lpo[kk] = ElemTraits<T>::to_float(sT[lab[kk - 1]]) * B200_LOG2E;
+        park[kk] = ElemTraits<T>::to_float(sT[lab[kk - 1]]) * B200_LOG2E;
+      // Every thread of the group owns the vectors gtid + GT*u; the first nfull of them exist for
+      // every thread (no bounds checks in the unrolled loops), at most one more for some.
+      auto drive = [&](auto pass) {
+        int u = 0;
+        for (; u + 4 <= nfull; u += 4) pass(gtid + GT * u, std::integral_constant<int, 4>{});
+        for (; u < nfull; ++u) pass(gtid + GT * u, std::integral_constant<int, 1>{});
+        if (tail) pass(gtid + GT * nfull, std::integral_constant<int, 1>{});
+      };
       // pass 1: row maximum (packed for the 16-bit types)
       uint32_t m0 = neg_inf_word<T>(), m1 = m0;
-      for (int j0 = gtid; j0 < nvec; j0 += 4 * GT) {
-        uint4 q[4];
+      drive([&](int j0, auto n_) {
+        constexpr int N = decltype(n_)::value;
+        uint4 q[N];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int j = j0 + GT * u;
-          const uint32_t ni = neg_inf_word<T>();
-          q[u] = j < nvec ? s4[j] : make_uint4(ni, ni, ni, ni);
-        }
+        for (int u = 0; u < N; ++u) q[u] = s4[j0 + GT * u];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) vmax_acc<T>(q[u], m0, m1);
-      }
+        for (int u = 0; u < N; ++u) vmax_acc<T>(q[u], m0, m1);
+      });
       float mx = warp_max(vmax_final<T>(m0, m1));
       if (G > 1) {
         if (lane == 0) s_mx[warp] = mx;
@@ -244,17 +260,13 @@ ctc_stream_kernel(LossParams p, int nslots, int slot_bytes) {
       const float ml = mx * B200_LOG2E - StreamMid<T>::kBias;
       // pass 2: exponentials, summed in fp32 and kept in place
       float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-      for (int j0 = gtid; j0 < nvec; j0 += 4 * GT) {
-        uint4 q[4];
+      drive([&](int j0, auto n_) {
+        constexpr int N = decltype(n_)::value;
+        uint4 q[N];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int j = j0 + GT * u;
-          const uint32_t ni = neg_inf_word<T>();
-          q[u] = j < nvec ? s4[j] : make_uint4(ni, ni, ni, ni);
-        }
+        for (int u = 0; u < N; ++u) q[u] = s4[j0 + GT * u];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int j = j0 + GT * u;
+        for (int u = 0; u < N; ++u) {
           float f[PER];
           unpack16<T>(q[u], f);
 #pragma unroll
@@ -265,9 +277,9 @@ ctc_stream_kernel(LossParams p, int nslots, int slot_bytes) {
             f[e + 3] = ex2f(fmaf(f[e + 3], B200_LOG2E, -ml));
             s0 += f[e]; s1 += f[e + 1]; s2 += f[e + 2]; s3 += f[e + 3];
           }
-          if (j < nvec) s4[j] = StreamMid<T>::pack(f);
+          s4[j0 + GT * u] = StreamMid<T>::pack(f);
         }
-      }
+      });
       float ssum = warp_sum((s0 + s1) + (s2 + s3));
       if (G > 1) {
         if (lane == 0) s_sm[warp] = ssum;
@@ -283,29 +295,27 @@ ctc_stream_kernel(LossParams p, int nslots, int slot_bytes) {
 #pragma unroll
       for (int g = 0; g < kStreamGather; ++g) {
         const int kk = gtid + GT * g;
-        if (kk <= L) lpo[kk] = fmaxf(fmaf(xg[g], B200_LOG2E, -l2), B200_NEG);
+        if (kk <= L) st_relaxed_f32(lpo + kk, fmaxf(fmaf(xg[g], B200_LOG2E, -l2), B200_NEG));
       }
-      for (int kk = gtid + GT * kStreamGather; kk <= L; kk += GT) lpo[kk] = fmaxf(lpo[kk] - l2, B200_NEG);
+      for (int kk = gtid + GT * kStreamGather; kk <= L; kk += GT)
+        st_relaxed_f32(lpo + kk, fmaxf(park[kk] - l2, B200_NEG));
       if (gtid == 0) p.ws.lse2[row] = l2;
       // pass 3: e * (w / sum) in the output type, in place
       const float scale = wgt / ssum;
-      for (int j0 = gtid; j0 < nvec; j0 += 4 * GT) {
-        uint4 q[4];
+      drive([&](int j0, auto n_) {
+        constexpr int N = decltype(n_)::value;
+        uint4 q[N];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int j = j0 + GT * u;
-          q[u] = j < nvec ? s4[j] : make_uint4(0, 0, 0, 0);
-        }
+        for (int u = 0; u < N; ++u) q[u] = s4[j0 + GT * u];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int j = j0 + GT * u;
+        for (int u = 0; u < N; ++u) {
           float f[PER];
           StreamMid<T>::unpack(q[u], f);
 #pragma unroll
           for (int e = 0; e < PER; ++e) f[e] *= scale;
-          if (j < nvec) s4[j] = pack16<T>(f);
+          s4[j0 + GT * u] = pack16<T>(f);
         }
-      }
+      });
       fence_proxy_async();
       if (G > 1) group_sync(bar_id, GT); else __syncwarp();
       if (gtid == 0) {
@@ -347,8 +357,8 @@ static int launch_stream_t(const LossParams& p, const StreamCfg& c, cudaStream_t
   if (g > nrows) g = nrows;
   auto go = [&](auto kern) -> int {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem));
-    kern<<<(unsigned)g, (kStreamWarps + 1) * 32, c.smem, st>>>(p, c.nslots, c.slot_bytes);
-    B200_CUDA(cudaGetLastError());
+    B200_CUDA(launch_kernel(kern, dim3((unsigned)g), dim3((kStreamWarps + 1) * 32), (size_t)c.smem, st, true, p,
+                            c.nslots, c.slot_bytes));
     return B200_OK;
   };
   if (c.group == 1) return go(ctc_stream_kernel<T, 1>);

@@ -49,6 +49,22 @@ __device__ __forceinline__ float clamp_int_f(float x) {  // integer-valued, safe
   return fminf(fmaxf(rintf(x), -4194304.0f), 4194304.0f);
 }
 
+// Final value of utterance b; the CTA that delivers the last one also sums them (fixed order:
+// the sum is deterministic).
+__device__ __forceinline__ void sweep_finish_nll(const LossParams& p, int b, float nll) {
+  p.nll[b] = nll;
+  p.ws.nll_ws[b] = nll;
+  if (p.loss_sum == nullptr) return;
+  __threadfence();
+  const int done = atomicAdd(p.ws.bad + 4, 1);
+  if (done == (p.b1 - p.b0) - 1) {
+    __threadfence();
+    float s = 0.f;
+    for (int o = p.b0; o < p.b1; ++o) s += ld_cg_f32(p.nll + o);
+    *p.loss_sum = s;
+  }
+}
+
 template <int MAXT> struct SweepRings {
   // hand-off ring in frames: > (maximum skew = delay <= MAXT/32 chunks) + 2 chunks; level ring in
   // chunks: > 2 * delay + 2.  Powers of two so that the ring indices are masks.
@@ -63,7 +79,8 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
   extern __shared__ __align__(16) unsigned char sw_smem[];
   constexpr int kR = SweepRings<MAXT>::kR, kWR = SweepRings<MAXT>::kWR;
   static_assert(CHF == SweepRings<MAXT>::kCHF, "chunk size");
-  const int b = p.b0 + blockIdx.x;
+  pdl_launch_dependents();  // the occupancy kernel may be staged; it waits for this grid to finish
+  const int b = p.ws.order[p.b0 + blockIdx.x];
   const int d = blockIdx.y;
   const int Tb = min((int)p.ilen[b], (int)p.T);
   const int L = (int)p.olen[b];
@@ -80,12 +97,14 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
 
   if (Tb <= 0) {
     if (i == 0) {
-      if (d == 0) p.nll[b] = p.ws.nll_ws[b] = (L == 0) ? 0.0f : __int_as_float(0x7f800000);
+      if (d == 0) sweep_finish_nll(p, b, (L == 0) ? 0.0f : __int_as_float(0x7f800000));
       else p.ws.logz_beta[b] = (L == 0) ? 0.0f : B200_NEG;
     }
+    pdl_wait();
     return;
   }
   for (int k = i; k < nw * kR + kWR * nw; k += blockDim.x) s_bnd[k].tag = -1;
+  if (!p.wait_rows) pdl_wait();  // staged under the kernel that produces lpg: it is complete from here
   __syncthreads();
   if (warp >= nwa) return;
 
@@ -160,12 +179,21 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     }
     return corr;
   };
+  // lpg word that may not have been produced yet (fused call: NaN until the stream kernel writes it)
+  const bool spin = p.wait_rows != 0;
+  auto load_lp = [&](const float* q) -> float {
+    float v = ld_relaxed_f32(q);
+    if (spin) {
+      while (v != v) { __nanosleep(128); v = ld_relaxed_f32(q); }
+    }
+    return v;
+  };
   // generic (slow) chunk: the first chunk and a trailing partial chunk; reads lpg directly
   auto slow_chunk = [&](int c, int n) {
     const int f0 = c * CHF;
     float corr = 0.f;
     if (c == 0) {
-      if (Tb > 1) dstep = clamp_int_f(floorf(ld_nc_f32(lp0 + lstep)));
+      if (Tb > 1) dstep = clamp_int_f(floorf(load_lp(lp0 + lstep)));
       if (lane31) s_hist[0] = 0;
     } else {
       corr = chunk_begin(c, n);
@@ -173,8 +201,8 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     for (int f = 0; f < n; ++f) {
       const int fr = f0 + f;
       const float* rowp = lp0 + (int64_t)fr * lstep;
-      const float lb_t = ld_nc_f32(rowp);
-      const float ll_t = has_label ? ld_nc_f32(rowp + kcol) : B200_NEG;
+      const float lb_t = load_lp(rowp);
+      const float ll_t = has_label ? load_lp(rowp + kcol) : B200_NEG;
       if (fr == 0) {
         // frame 0: only the first blank and the first label are reachable
         if (i == 0) { ab = lb_t; al = ll_t; }
@@ -197,14 +225,25 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     const float* rowp = lp0 + (int64_t)(c * CHF) * lstep;
 #pragma unroll
     for (int f = 0; f < CHF; ++f) {
-      xb[f] = ld_nc_f32(rowp);
-      xl[f] = has_label ? ld_nc_f32(rowp + kcol) : B200_NEG;  // a missing label state stays at log(0)
+      xb[f] = ld_relaxed_f32(rowp);
+      xl[f] = has_label ? ld_relaxed_f32(rowp + kcol) : B200_NEG;  // a missing label state stays at log(0)
       rowp += lstep;
     }
   };
   // full chunk c >= 1: straight-line code, no branch inside the frames
-  auto fast_chunk = [&](int c, const float(&xb)[CHF], const float(&xl)[CHF]) {
+  auto fast_chunk = [&](int c, float(&xb)[CHF], float(&xl)[CHF]) {
     const int f0 = c * CHF;
+    if (spin) {
+      // the prefetch may have run ahead of the stream kernel: reload until every word is a number
+      for (;;) {
+        bool missing = false;
+#pragma unroll
+        for (int f = 0; f < CHF; ++f) missing = missing || (xb[f] != xb[f]) || (xl[f] != xl[f]);
+        if (!__any_sync(0xffffffffu, missing)) break;
+        __nanosleep(128);
+        load_chunk(c, xb, xl);
+      }
+    }
     const float corr = chunk_begin(c, CHF);
     float bn[CHF];
 #pragma unroll
@@ -256,9 +295,11 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     const float z = lse2(s_fin[0], s_fin[1]);
     const bool feasible = z > -1.0e29f;
     const float logz2 = z + (float)csum;
-    if (d == 0) p.nll[b] = p.ws.nll_ws[b] = feasible ? -B200_LN2 * logz2 : __int_as_float(0x7f800000);
+    if (d == 0) sweep_finish_nll(p, b, feasible ? -B200_LN2 * logz2 : __int_as_float(0x7f800000));
     else p.ws.logz_beta[b] = feasible ? logz2 : B200_NEG;
   }
+  // this grid must not be seen as finished before the stream kernel it ran under
+  if (p.wait_rows) pdl_wait();
 }
 
 template <int MAXT>
@@ -268,19 +309,23 @@ static size_t sweep_smem_bytes(int nw) {
 }
 
 template <int CHF, int MAXT>
-static int launch_sweep_t(const LossParams& p, int threads, cudaStream_t st) {
-  const size_t smem = sweep_smem_bytes<MAXT>(threads / 32);
+static int launch_sweep_t(const LossParams& p, int threads, cudaStream_t st, bool pdl) {
+  size_t smem = sweep_smem_bytes<MAXT>(threads / 32);
+  // A sweep CTA is one latency chain: give it an SM of its own whenever the grid fits that way.
+  // (Staged under the previous kernel by PDL, CTAs would otherwise pile up on the SMs that free
+  // up first.)  Asking for more than half of the shared memory caps residency at one CTA per SM.
+  if (2 * (p.b1 - p.b0) <= num_sms() && smem < 116 * 1024) smem = 116 * 1024;
   auto kern = ctc_sweep_kernel<CHF, MAXT>;
   if (smem > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<dim3((unsigned)(p.b1 - p.b0), 2), threads, smem, st>>>(p);
-  B200_CUDA(cudaGetLastError());
+  B200_CUDA(launch_kernel(kern, dim3((unsigned)(p.b1 - p.b0), 2), dim3(threads), smem, st, pdl, p));
   return B200_OK;
 }
 
-static int launch_sweep(const LossParams& p, cudaStream_t st) {
+// pdl: staged under the stream kernel of the same call (p.wait_rows must be set)
+static int launch_sweep(const LossParams& p, cudaStream_t st, bool pdl = false) {
   const int threads = (int)align_up((size_t)(p.Lmax + 1), 32);
-  if (threads <= 256) return launch_sweep_t<8, 256>(p, threads, st);
-  return launch_sweep_t<4, 1024>(p, threads, st);
+  if (threads <= 256) return launch_sweep_t<8, 256>(p, threads, st, pdl);
+  return launch_sweep_t<4, 1024>(p, threads, st, pdl);
 }
 
 }  // namespace b200
