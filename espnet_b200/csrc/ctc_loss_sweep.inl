@@ -151,6 +151,10 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
   // start of chunk c >= 1 (n frames): publish this warp's level, consume everybody's of chunk
   // c - delay, derive the integer removals of this chunk (dstep per frame, corr once)
   auto chunk_begin = [&](int c, int n) -> float {
+    // levels are published and consumed every kP-th chunk only (this is per-chunk overhead on the
+    // critical path of every warp); dstep holds in between
+    constexpr int kP = 2;
+    if (c % kP) return 0.f;
     float corr = 0.f;
     const float wm = warp_max_redux(fmaxf(ab, al));
     if (lane31) {
@@ -158,8 +162,9 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
       s_hist[c & (kWR - 1)] = csum;
     }
     __syncwarp();
-    const int cm = c - delay;
-    if (cm >= 1) {
+    const int delay_p = (delay + kP - 1) / kP * kP;
+    const int cm = c - delay_p;
+    if (cm >= kP) {
       Tagged e;
       e.v = B200_NEG; e.tag = cm;
       if (lane < nwa) {
@@ -171,11 +176,13 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
       const int sm = s_hist[cm & (kWR - 1)];
       // uncentred level y = x + S; drift per frame from two consecutive measurements
       float delta = dstep;
-      if (have_prev) delta = (xm - xprev + (float)(sm - sprev)) * (1.0f / CHF);
+      if (have_prev) delta = (xm - xprev + (float)(sm - sprev)) * (1.0f / (kP * CHF));
       xprev = xm; sprev = sm; have_prev = true;
-      const float xhat = xm + (float)(sm - csum) + delta * (float)(CHF * delay);  // level now
+      const float xhat = xm + (float)(sm - csum) + delta * (float)(CHF * delay_p);  // level now
+      // remove, over the next kP chunks, what brings the level back to zero at their end
+      const float horizon = (float)(n == CHF ? kP * CHF : n);
       dstep = clamp_int_f(delta);
-      corr = clamp_int_f(clamp_int_f(xhat + delta * (float)n) - dstep * (float)n);
+      corr = clamp_int_f(clamp_int_f(xhat + delta * horizon) - dstep * horizon);
     }
     return corr;
   };
@@ -198,24 +205,38 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     } else {
       corr = chunk_begin(c, n);
     }
-    for (int f = 0; f < n; ++f) {
-      const int fr = f0 + f;
-      const float* rowp = lp0 + (int64_t)fr * lstep;
-      const float lb_t = load_lp(rowp);
-      const float ll_t = has_label ? load_lp(rowp + kcol) : B200_NEG;
-      if (fr == 0) {
-        // frame 0: only the first blank and the first label are reachable
-        if (i == 0) { ab = lb_t; al = ll_t; }
-        if (lane31) sts_tagged(&bdst[0], al, 0);
-        if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
-        outp += ostep;
-      } else {
-        Tagged e;
-        e.v = B200_NEG; e.tag = fr - 1;
-        if (poll) {
-          do { e = lds_tagged(&bsrc[(fr - 1) & (kR - 1)]); } while (e.tag != fr - 1);
+    // all loads of the chunk first (one memory latency, not one per frame)
+    float sb[CHF], sl[CHF];
+#pragma unroll
+    for (int f = 0; f < CHF; ++f) {
+      const float* rowp = lp0 + (int64_t)(f0 + min(f, n - 1)) * lstep;
+      sb[f] = ld_relaxed_f32(rowp);
+      sl[f] = has_label ? ld_relaxed_f32(rowp + kcol) : B200_NEG;
+    }
+#pragma unroll
+    for (int f = 0; f < CHF; ++f) {
+      if (f < n) {
+        const int fr = f0 + f;
+        float lb_t = sb[f], ll_t = sl[f];
+        if (spin) {
+          const float* rowp = lp0 + (int64_t)fr * lstep;
+          if (lb_t != lb_t) lb_t = load_lp(rowp);
+          if (ll_t != ll_t) ll_t = load_lp(rowp + kcol);
         }
-        frame(lb_t, ll_t, e.v, dstep + (f == 0 ? corr : 0.f), fr);
+        if (fr == 0) {
+          // frame 0: only the first blank and the first label are reachable
+          if (i == 0) { ab = lb_t; al = ll_t; }
+          if (lane31) sts_tagged(&bdst[0], al, 0);
+          if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
+          outp += ostep;
+        } else {
+          Tagged e;
+          e.v = B200_NEG; e.tag = fr - 1;
+          if (poll) {
+            do { e = lds_tagged(&bsrc[(fr - 1) & (kR - 1)]); } while (e.tag != fr - 1);
+          }
+          frame(lb_t, ll_t, e.v, dstep + (f == 0 ? corr : 0.f), fr);
+        }
       }
     }
     csum += (n - (c == 0 ? 1 : 0)) * (int)dstep + (int)corr;
