@@ -241,7 +241,8 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     }
     csum += (n - (c == 0 ? 1 : 0)) * (int)dstep + (int)corr;
   };
-  // registers of one full chunk, loaded three chunks ahead of their use
+  const int nfull = Tb / CHF;  // chunks 1 .. nfull-1 are full and take the fast path
+  // registers of one full chunk, loaded two chunks ahead of their use
   auto load_chunk = [&](int c, float(&xb)[CHF], float(&xl)[CHF]) {
     const float* rowp = lp0 + (int64_t)(c * CHF) * lstep;
 #pragma unroll
@@ -252,7 +253,10 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     }
   };
   // full chunk c >= 1: straight-line code, no branch inside the frames
-  auto fast_chunk = [&](int c, float(&xb)[CHF], float(&xl)[CHF]) {
+  // nb / nl: the register set that is free during this chunk; it receives chunk c + 2 right after
+  // the first use of xb / xl, so that a whole chunk of time lies between the issue of any load and
+  // the next wait on a load scoreboard (ptxas may give several load batches the same scoreboard)
+  auto fast_chunk = [&](int c, float(&xb)[CHF], float(&xl)[CHF], float(&nb)[CHF], float(&nl)[CHF]) {
     const int f0 = c * CHF;
     if (spin) {
       // the prefetch may have run ahead of the stream kernel: reload until every word is a number
@@ -265,6 +269,12 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
         load_chunk(c, xb, xl);
       }
     }
+    // first use of this chunk's registers (waits for their loads), then the prefetch
+    float first = xb[0] + xl[0];
+#pragma unroll
+    for (int f = 1; f < CHF; ++f) first += xb[f] + xl[f];
+    asm volatile("" ::"f"(first));
+    if (c + 2 < nfull) load_chunk(c + 2, nb, nl);
     const float corr = chunk_begin(c, CHF);
     float bn[CHF];
 #pragma unroll
@@ -287,22 +297,17 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     csum += CHF * (int)dstep + (int)corr;
   };
 
-  const int nfull = Tb / CHF;  // chunks 1 .. nfull-1 are full and take the fast path
   float rb0[CHF], rl0[CHF], rb1[CHF], rl1[CHF], rb2[CHF], rl2[CHF];
   if (1 < nfull) load_chunk(1, rb0, rl0);
   if (2 < nfull) load_chunk(2, rb1, rl1);
-  if (3 < nfull) load_chunk(3, rb2, rl2);
   slow_chunk(0, min(CHF, Tb));
   int c = 1;
   while (c < nfull) {
-    fast_chunk(c, rb0, rl0);
-    if (c + 3 < nfull) load_chunk(c + 3, rb0, rl0);
+    fast_chunk(c, rb0, rl0, rb2, rl2);
     if (++c >= nfull) break;
-    fast_chunk(c, rb1, rl1);
-    if (c + 3 < nfull) load_chunk(c + 3, rb1, rl1);
+    fast_chunk(c, rb1, rl1, rb0, rl0);
     if (++c >= nfull) break;
-    fast_chunk(c, rb2, rl2);
-    if (c + 3 < nfull) load_chunk(c + 3, rb2, rl2);
+    fast_chunk(c, rb2, rl2, rb1, rl1);
     ++c;
   }
   if (nfull >= 1 && Tb > nfull * CHF) slow_chunk(nfull, Tb - nfull * CHF);
