@@ -25,6 +25,8 @@ SIGNATURES = {
                                       _i64, _int, _vp, _f32, _vp, _i64, _i64, _vp, _sz, _vp]),
     "b200_ctc_loss_fwd_bwd": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp,
                                      _i64, _int, _vp, _f32, _vp, _vp, _vp, _i64, _i64, _vp, _sz, _vp]),
+    "b200_ctc_loss_stream_pass": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp,
+                                         _i64, _int, _vp, _f32, _vp, _i64, _i64, _vp, _sz, _vp]),
     "b200_ctc_prefix_init": (_int, [_vp, _vp, _i64, _i64, _i64, _int, _vp, _vp, _vp]),
     "b200_ctc_prefix_work_floats": (_sz, [_i64, _i64]),
     "b200_ctc_prefix_score": (_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _int, _int, _vp, _vp,

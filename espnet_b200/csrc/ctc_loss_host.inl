@@ -148,7 +148,8 @@ static int launch_prep(const LossParams& p, cudaStream_t st) {
 
 // One pass over the logits (stream), the two lattice sweeps, and the column patch.
 // Returns false in *done when the shape needs the general three-pass path.
-static int run_fused(LossParams p, int dtype, float* loss_sum, cudaStream_t st, bool* done) {
+static int run_fused(LossParams p, int dtype, float* loss_sum, cudaStream_t st, bool* done,
+                     bool stream_only = false) {
   *done = false;
   const int es = elem_size(dtype);
   StreamCfg sc;
@@ -169,6 +170,7 @@ static int run_fused(LossParams p, int dtype, float* loss_sum, cudaStream_t st, 
   // the sweeps
   rc = launch_stream(p, dtype, sc, st);
   if (rc) return rc;
+  if (stream_only) { *done = true; return B200_OK; }
   rc = launch_sweep(p, st, true);
   if (rc) return rc;
   rc = launch_patch(p, dtype, st);
@@ -259,4 +261,26 @@ extern "C" int b200_ctc_loss_fwd_bwd(const void* logits, int dtype, int64_t T, i
   return b200_ctc_loss_backward(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen,
                                 Lmax, blank, grad_weight, grad_scale, grad_logits, gstride_t, gstride_b,
                                 workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200_ctc_loss_stream_pass(const void* logits, int dtype, int64_t T, int64_t B, int64_t V,
+                                         int64_t stride_t, int64_t stride_b, const int64_t* targets,
+                                         const int64_t* tgt_offsets, const int64_t* ilen, const int64_t* olen,
+                                         int64_t Lmax, int blank, const float* grad_weight, float grad_scale,
+                                         void* grad_logits, int64_t gstride_t, int64_t gstride_b,
+                                         void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_common(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
+                        blank, workspace, workspace_bytes);
+  if (rc) return rc;
+  B200_CHECK_ARG(grad_logits != nullptr, B200_ERR_INVALID_ARGUMENT, "grad_logits is null");
+  LossParams p = make_params(logits, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
+                             blank, nullptr, workspace);
+  p.grad = grad_logits;
+  p.gstride_t = gstride_t; p.gstride_b = gstride_b;
+  p.grad_weight = grad_weight; p.grad_scale = grad_scale;
+  bool done = false;
+  rc = run_fused(p, dtype, nullptr, (cudaStream_t)stream, &done, true);
+  if (rc) return rc;
+  B200_CHECK_ARG(done, B200_ERR_UNSUPPORTED_SHAPE, "this shape runs on the three-pass path (no one-pass stream stage)");
+  return B200_OK;
 }

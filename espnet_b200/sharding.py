@@ -1,0 +1,34 @@
+"""Utterance sharding of the CTC loss across the GPUs of one box.
+
+The path shards by utterance with no data-path collective: every rank runs the
+kernels on its own contiguous block of utterances and the only message is one all-reduce of
+two floats, (sum of nll, number of utterances), exactly what the reference's
+``recursive_average`` does with (loss * weight, weight)
+(``espnet2/torch_utils/recursive_op.py:24-53``).
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(n_utt, rank, world):
+    """Contiguous block [lo, hi) of rank `rank`; blocks differ by at most one utterance."""
+    if not 0 <= rank < world:
+        raise ValueError(f"rank {rank} outside [0, {world})")
+    base, rem = divmod(n_utt, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def allreduce_loss(nll_sum, n_utt, group=None, out=None):
+    """Global (mean loss, number of utterances) from this rank's (sum of nll, utterance count).
+
+    nll_sum: 0-dim or 1-element tensor on the rank's device (NCCL: cuda, gloo: cpu).  One
+    all-reduce(SUM) of a 2-element fp32 buffer; without an initialised process group the
+    local values are returned unchanged.
+    """
+    buf = out if out is not None else torch.empty(2, dtype=torch.float32, device=nll_sum.device)
+    buf[0:1].copy_(nll_sum.reshape(1))
+    buf[1] = float(n_utt)
+    if dist.is_available() and dist.is_initialized():
+        dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+    return buf[0] / buf[1], buf[1]

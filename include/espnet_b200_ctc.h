@@ -117,8 +117,12 @@ int b200_ctc_loss_backward(const void* logits, int dtype,
                            void* grad_logits, int64_t gstride_t, int64_t gstride_b,
                            void* workspace, size_t workspace_bytes, void* stream);
 
-/* _forward followed by _backward in one call (training with a known upstream
- * gradient, and the benchmark's "fwd+bwd" unit of work). */
+/* Forward and backward in one call (training with a known upstream gradient, and
+ * the benchmark's "fwd+bwd" unit of work).  When the vocabulary rows are 16-byte
+ * aligned and fit the shared-memory ring, the logits are read ONCE: the pass that
+ * computes the row statistics also writes grad_scale*grad_weight*softmax to
+ * grad_logits, and the lattice kernels then overwrite only the blank and label
+ * columns.  Other shapes run _forward followed by _backward. */
 int b200_ctc_loss_fwd_bwd(const void* logits, int dtype,
                           int64_t T, int64_t B, int64_t V,
                           int64_t stride_t, int64_t stride_b,
@@ -129,6 +133,21 @@ int b200_ctc_loss_fwd_bwd(const void* logits, int dtype,
                           float* nll, float* loss_sum,
                           void* grad_logits, int64_t gstride_t, int64_t gstride_b,
                           void* workspace, size_t workspace_bytes, void* stream);
+
+/* Measurement aid: ONLY the first stage of b200_ctc_loss_fwd_bwd (label prep + the
+ * one pass over the logits: row statistics, label gather into the workspace and
+ * grad_scale*grad_weight*softmax written to grad_logits).  bench.py times the
+ * dominant HBM kernel with it; the result is not a gradient.  Returns
+ * B200_ERR_UNSUPPORTED_SHAPE for shapes that _fwd_bwd runs on the three-pass path. */
+int b200_ctc_loss_stream_pass(const void* logits, int dtype,
+                              int64_t T, int64_t B, int64_t V,
+                              int64_t stride_t, int64_t stride_b,
+                              const int64_t* targets, const int64_t* tgt_offsets,
+                              const int64_t* ilen, const int64_t* olen,
+                              int64_t Lmax, int blank,
+                              const float* grad_weight, float grad_scale,
+                              void* grad_logits, int64_t gstride_t, int64_t gstride_b,
+                              void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------
  * CTC prefix scoring (CTCPrefixScoreTH)

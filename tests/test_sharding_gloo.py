@@ -1,0 +1,83 @@
+"""The N>1 path on CPU: two gloo ranks shard a batch by utterance, each computes the nll of its
+own block, and one 2-float all-reduce gives the global mean loss.  The per-rank
+nll here comes from the reference formula on CPU (no GPU in this test); what is under test is
+the sharding and the reduction."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from tests import _cases
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _nll(x, ilen, olen, ys):
+    tg = torch.cat([ys[i, : olen[i]] for i in range(x.shape[0])])
+    lp = x.double().transpose(0, 1).log_softmax(2)
+    return torch.nn.functional.ctc_loss(lp, tg, ilen, olen, reduction="none")
+
+
+def _worker(rank, world, port, n_utt, q):
+    from espnet_b200.sharding import allreduce_loss, shard_bounds
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    c = _cases.make_loss_case(n_utt, 40, 16, 8, seed=31)
+    lo, hi = shard_bounds(n_utt, rank, world)
+    nll = _nll(c["x"][lo:hi], c["ilen"][lo:hi], c["olen"][lo:hi], c["ys"][lo:hi])
+    mean, n = allreduce_loss(nll.sum().float(), hi - lo)
+    q.put((rank, lo, hi, float(mean), float(n)))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_utt", [6, 7])
+def test_two_ranks_reproduce_the_global_mean(n_utt):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n_utt, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    c = _cases.make_loss_case(n_utt, 40, 16, 8, seed=31)
+    ref = float(_nll(c["x"], c["ilen"], c["olen"], c["ys"]).sum()) / n_utt
+    assert res[0][1] == 0 and res[0][2] == res[1][1] and res[1][2] == n_utt   # blocks tile the batch
+    for r in res:
+        np.testing.assert_allclose(r[3], ref, rtol=1e-6)
+        assert r[4] == n_utt
+
+
+def test_shard_bounds_cover_everything():
+    from espnet_b200.sharding import shard_bounds
+
+    for n in (0, 1, 7, 64, 512):
+        for world in (1, 2, 3, 8):
+            edges = [shard_bounds(n, r, world) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == n
+            assert all(edges[k][1] == edges[k + 1][0] for k in range(world - 1))
+            sizes = [hi - lo for lo, hi in edges]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        shard_bounds(4, 2, 2)
+
+
+def test_allreduce_without_process_group_is_local():
+    from espnet_b200.sharding import allreduce_loss
+
+    mean, n = allreduce_loss(torch.tensor(12.0), 4)
+    assert float(mean) == 3.0 and float(n) == 4.0
