@@ -1,7 +1,191 @@
-// ctc_misc.cu -- greedy path and forced alignment: not built yet.
+// ctc_misc.cu -- greedy path (row argmax) and Viterbi forced alignment.
+//
+//   b200_ctc_greedy   espnet2/asr/ctc.py:103-111 / pytorch_backend/ctc.py:144-151 (CTC.argmax):
+//                     ids[b,t] = argmax_v logits[b,t,v], first maximum, NaN counts as the maximum
+//                     (torch.argmax).  One warp per row, 128-bit loads: the row is read once (HBM).
+//   b200_ctc_viterbi  espnet/nets/pytorch_backend/ctc.py:153-216 (CTC.forced_align): max instead of
+//                     log-sum-exp on the same lattice, float64 scores as the reference's numpy
+//                     arrays, candidates compared in the reference's order [s, s-1, s-2] with the
+//                     first maximum kept, including its wrap-around read of state -1 for s = 0.
 #include "common.cuh"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------ greedy
+// a is better than b: larger value, or equal value at a smaller index; NaN beats every number
+__device__ __forceinline__ bool arg_better(float va, int ia, float vb, int ib) {
+  const bool na = va != va, nb = vb != vb;
+  if (na || nb) return na && (!nb || ia < ib);
+  return va > vb || (va == vb && ia < ib);
+}
+
+constexpr int kGreedyWarps = 8;
+
+template <typename T, bool VEC>
+__global__ void __launch_bounds__(kGreedyWarps * 32) ctc_greedy_kernel(const T* __restrict__ logits, int64_t B, int64_t Tn,
+                                                                      int V, int64_t stride_b, int64_t stride_t,
+                                                                      int64_t* __restrict__ ids) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int PER = ElemTraits<T>::kPerVec;
+  const int64_t nrows = B * Tn;
+  const int nvec = (int)((int64_t)V * sizeof(T) / 16);
+  for (int64_t r = (int64_t)blockIdx.x * kGreedyWarps + warp; r < nrows; r += (int64_t)gridDim.x * kGreedyWarps) {
+    const T* src = logits + (r / Tn) * stride_b + (r % Tn) * stride_t;
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    if (VEC) {
+      const uint4* s4 = reinterpret_cast<const uint4*>(src);
+      for (int j0 = lane; j0 < nvec; j0 += 128) {
+        uint4 q[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int j = j0 + 32 * u;
+          q[u] = j < nvec ? ld_nc_v4(s4 + j) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int j = j0 + 32 * u;
+          if (j < nvec) {
+            float f[PER];
+            unpack16<T>(q[u], f);
+#pragma unroll
+            for (int e = 0; e < PER; ++e)
+              if (arg_better(f[e], j * PER + e, best, bi)) { best = f[e]; bi = j * PER + e; }
+          }
+        }
+      }
+    } else {
+      for (int v = lane; v < V; v += 32) {
+        const float x = ElemTraits<T>::to_float(src[v]);
+        if (arg_better(x, v, best, bi)) { best = x; bi = v; }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (arg_better(ov, oi, best, bi)) { best = ov; bi = oi; }
+    }
+    if (lane == 0) ids[r] = bi;
+  }
+}
+
+template <typename T>
+static int launch_greedy(const void* logits, int64_t B, int64_t Tn, int64_t V, int64_t stride_b, int64_t stride_t,
+                         int64_t* ids, cudaStream_t st) {
+  const int es = (int)sizeof(T);
+  const bool vec = (reinterpret_cast<uintptr_t>(logits) & 15) == 0 && (V * es) % 16 == 0 && (stride_b * es) % 16 == 0 &&
+                   (stride_t * es) % 16 == 0;
+  int64_t g = (B * Tn + kGreedyWarps - 1) / kGreedyWarps;
+  const int64_t cap = (int64_t)num_sms() * 8;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  if (vec)
+    ctc_greedy_kernel<T, true><<<(unsigned)g, kGreedyWarps * 32, 0, st>>>((const T*)logits, B, Tn, (int)V, stride_b,
+                                                                         stride_t, ids);
+  else
+    ctc_greedy_kernel<T, false><<<(unsigned)g, kGreedyWarps * 32, 0, st>>>((const T*)logits, B, Tn, (int)V, stride_b,
+                                                                          stride_t, ids);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+// ------------------------------------------------------------------------------ Viterbi
+constexpr double kVitLogZero = -100000000000.0;  // the reference's "log of zero"
+
+__device__ __forceinline__ int vit_ext(const int64_t* y, int blank, int s) { return (s & 1) ? (int)y[s >> 1] : blank; }
+
+// One CTA per utterance; scores of two consecutive frames ping-pong in shared memory.
+__global__ void __launch_bounds__(1024) ctc_viterbi_kernel(const float* __restrict__ lpz, int T, int V,
+                                                           const int64_t* __restrict__ y, int L, int blank,
+                                                           int64_t* __restrict__ align, int16_t* __restrict__ path) {
+  extern __shared__ double vit_delta[];  // [2][S]
+  const int S = 2 * L + 1;
+  double* cur = vit_delta;
+  double* nxt = vit_delta + S;
+  for (int s = threadIdx.x; s < S; s += blockDim.x) {
+    double v = kVitLogZero;
+    if (s < 2) v = (double)lpz[vit_ext(y, blank, s)];
+    cur[s] = v;
+  }
+  __syncthreads();
+  for (int t = 1; t < T; ++t) {
+    const float* row = lpz + (int64_t)t * V;
+    for (int s = threadIdx.x; s < S; s += blockDim.x) {
+      const int e = vit_ext(y, blank, s);
+      const int ncand = (e == blank || s < 2 || e == vit_ext(y, blank, s - 2)) ? 2 : 3;
+      int best_s = s;
+      double best = cur[s];
+      for (int j = 1; j < ncand; ++j) {
+        const int ps = s - j;
+        const double v = cur[ps < 0 ? ps + S : ps];  // the reference reads logdelta[t-1, -1] for s = 0
+        if (v > best) { best = v; best_s = ps; }
+      }
+      nxt[s] = best + (double)row[e];
+      path[(int64_t)t * S + s] = (int16_t)best_s;
+    }
+    __syncthreads();
+    double* tmp = cur; cur = nxt; nxt = tmp;
+  }
+  if (threadIdx.x == 0) {
+    // back-trace (T dependent reads of what this CTA wrote)
+    const double a = cur[S - 1];
+    const double b = cur[(S - 2) < 0 ? S - 2 + S : S - 2];
+    int st = (a >= b) ? S - 1 : S - 2;
+    for (int t = T - 1; t >= 0; --t) {
+      const int idx = st < 0 ? st + S : st;
+      align[t] = vit_ext(y, blank, idx);
+      if (t > 0) st = path[(int64_t)t * S + idx];
+    }
+  }
+}
+
+}  // namespace b200
+
 using namespace b200;
-#define STUB(name) do { set_error(name " is not implemented yet"); return B200_ERR_UNSUPPORTED_SHAPE; } while (0)
-extern "C" int b200_ctc_greedy(const void*, int, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t*, void*) { STUB("b200_ctc_greedy"); }
-extern "C" size_t b200_ctc_viterbi_work_bytes(int64_t, int64_t) { return 0; }
-extern "C" int b200_ctc_viterbi(const float*, int64_t, int64_t, const int64_t*, int64_t, int, int64_t*, void*, size_t, void*) { STUB("b200_ctc_viterbi"); }
+
+extern "C" int b200_ctc_greedy(const void* logits, int dtype, int64_t B, int64_t T, int64_t V, int64_t stride_b,
+                               int64_t stride_t, int64_t* ids, void* stream) {
+  B200_CHECK_ARG(logits && ids, B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(B >= 1 && T >= 1 && V >= 1 && V < (1ll << 30), B200_ERR_INVALID_ARGUMENT,
+                 "need B>=1, T>=1, 1<=V<2^30, got B=%lld T=%lld V=%lld", (long long)B, (long long)T, (long long)V);
+  B200_CHECK_ARG(stride_b >= 0 && stride_t >= 0, B200_ERR_INVALID_ARGUMENT, "negative stride");
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (dtype) {
+    case B200_F32: return launch_greedy<float>(logits, B, T, V, stride_b, stride_t, ids, st);
+    case B200_BF16: return launch_greedy<__nv_bfloat16>(logits, B, T, V, stride_b, stride_t, ids, st);
+    case B200_F16: return launch_greedy<__half>(logits, B, T, V, stride_b, stride_t, ids, st);
+  }
+  set_error("dtype must be B200_F32, B200_BF16 or B200_F16, got %d", dtype);
+  return B200_ERR_INVALID_ARGUMENT;
+}
+
+extern "C" size_t b200_ctc_viterbi_work_bytes(int64_t T, int64_t L) {
+  if (T < 1 || L < 0) return 0;
+  return (size_t)T * (size_t)(2 * L + 1) * sizeof(int16_t);
+}
+
+extern "C" int b200_ctc_viterbi(const float* lpz, int64_t T, int64_t V, const int64_t* y, int64_t L, int blank,
+                                int64_t* align, void* work, size_t work_bytes, void* stream) {
+  B200_CHECK_ARG(lpz && align && work && (y || L == 0), B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(T >= 1 && V >= 1 && L >= 0 && blank >= 0 && blank < V, B200_ERR_INVALID_ARGUMENT,
+                 "need T>=1, V>=1, L>=0, 0<=blank<V, got T=%lld V=%lld L=%lld blank=%d", (long long)T, (long long)V,
+                 (long long)L, blank);
+  B200_CHECK_ARG(2 * L + 1 <= 32767, B200_ERR_UNSUPPORTED_SHAPE,
+                 "L=%lld: back-pointers are int16 as in the reference (2L+1 <= 32767)", (long long)L);
+  B200_CHECK_ARG(T < (1ll << 31), B200_ERR_UNSUPPORTED_SHAPE, "T too large");
+  B200_CHECK_ARG(work_bytes >= b200_ctc_viterbi_work_bytes(T, L), B200_ERR_WORKSPACE_TOO_SMALL,
+                 "work has %zu bytes, need %zu", work_bytes, b200_ctc_viterbi_work_bytes(T, L));
+  const int S = (int)(2 * L + 1);
+  const size_t smem = 2 * (size_t)S * sizeof(double);
+  B200_CHECK_ARG(smem <= (size_t)max_smem_optin(), B200_ERR_UNSUPPORTED_SHAPE,
+                 "L=%lld needs %zu bytes of shared memory", (long long)L, smem);
+  if (smem > 48 * 1024)
+    B200_CUDA(cudaFuncSetAttribute(ctc_viterbi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int threads = (S + 31) / 32 * 32;
+  if (threads > 1024) threads = 1024;
+  ctc_viterbi_kernel<<<1, threads, smem, (cudaStream_t)stream>>>(lpz, (int)T, (int)V, y, (int)L, blank, align,
+                                                                 (int16_t*)work);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}

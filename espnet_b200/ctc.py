@@ -14,6 +14,7 @@ import numpy as np
 import torch
 import torch.nn.functional as F
 
+from .ctc_align import ctc_argmax, ctc_forced_align
 from .ctc_loss import ctc_nll
 
 
@@ -118,6 +119,8 @@ class CTC(torch.nn.Module):
 
     def argmax(self, hs_pad):
         """argmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax)."""
+        if self.ctc_type == "b200" and hs_pad.is_cuda:
+            return ctc_argmax(self.ctc_lo(hs_pad))
         return torch.argmax(self.ctc_lo(hs_pad), dim=2)
 
 
@@ -197,7 +200,19 @@ class CTCEspnet1(torch.nn.Module):
         return F.log_softmax(self.ctc_lo(hs_pad), dim=2)
 
     def argmax(self, hs_pad):
+        if self.ctc_type == "b200" and hs_pad.is_cuda:
+            return ctc_argmax(self.ctc_lo(hs_pad))
         return torch.argmax(self.ctc_lo(hs_pad), dim=2)
+
+    def forced_align(self, h, y, blank_id=0):
+        """Best alignment of the id sequence y (L,) to the hidden states h (T, D): a list of T ids
+        (espnet/nets/pytorch_backend/ctc.py:153-216; on the b200 path the Viterbi recursion runs
+        in ``b200_ctc_viterbi`` instead of a numpy double loop)."""
+        lpz = self.log_softmax(h)
+        lpz = lpz.squeeze(0)
+        if self.ctc_type != "b200":
+            raise NotImplementedError('forced_align is provided for ctc_type="b200" only')
+        return ctc_forced_align(lpz, y, blank_id)
 
 
 def ctc_for(args, odim, reduce=True):

@@ -205,15 +205,17 @@ int b200_ctc_prefix_select(const float* x, int64_t B, int64_t T, int64_t V,
  * Greedy path and forced alignment
  * ------------------------------------------------------------------------ */
 
-/* ids[b,t] = argmax_v logits[b,t,v] (first maximum), int64, for a (B,T,V) view
- * with element strides (stride_b, stride_t, 1). */
+/* ids[b,t] = argmax_v logits[b,t,v] (first maximum; a NaN counts as the maximum,
+ * as torch.argmax), int64 (B,T) contiguous, for a (B,T,V) view with element
+ * strides (stride_b, stride_t, 1). */
 int b200_ctc_greedy(const void* logits, int dtype, int64_t B, int64_t T, int64_t V,
                     int64_t stride_b, int64_t stride_t, int64_t* ids, void* stream);
 
 /* Viterbi alignment of one utterance: lpz fp32 (T,V) log-probs, y int64 (L,),
  * align int64 (T,) out: the label (or blank) emitted at each frame.
- * work: (T * (2L+1)) int16 back-pointers + 2*(2L+1) doubles, see
- * b200_ctc_viterbi_work_bytes. */
+ * Scores are float64 and candidates are compared in the reference's order
+ * (first maximum kept), so the alignment is the reference's bit for bit.
+ * work: T * (2L+1) int16 back-pointers (b200_ctc_viterbi_work_bytes). */
 size_t b200_ctc_viterbi_work_bytes(int64_t T, int64_t L);
 int b200_ctc_viterbi(const float* lpz, int64_t T, int64_t V,
                      const int64_t* y, int64_t L, int blank,
