@@ -113,18 +113,23 @@ def ctc_nll(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0):
 
 
 def ctc_loss_fwd_bwd(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, grad_weight=None,
-                     grad_scale=1.0, grad_out=None, plan=None):
+                     grad_scale=1.0, grad_out=None, plan=None, nll_out=None, loss_sum_out=None):
     """One fused call: returns (nll (B,), loss_sum (1,), grad (T,B,V) in logits' dtype).
 
     grad = grad_scale * grad_weight[b] * d nll_b / d logits.  This is the unit of work of
     ``bench.py`` (CTC loss fwd+bwd) and what a trainer with a known upstream scale uses.
+    nll_out (B,) / loss_sum_out (1,) fp32: caller-owned outputs, e.g. a slot of
+    ``sharding.LossLedger`` (no allocation and no copy kernel per call).
     """
     logits = _prep_logits(logits)
     if plan is None:
         plan = _Plan(logits, targets, tgt_offsets, ilen, olen, lmax, blank)
     dev = logits.device
-    nll = torch.empty(plan.B, dtype=torch.float32, device=dev)
-    loss_sum = torch.empty(1, dtype=torch.float32, device=dev)
+    nll = nll_out if nll_out is not None else torch.empty(plan.B, dtype=torch.float32, device=dev)
+    loss_sum = loss_sum_out if loss_sum_out is not None else torch.empty(1, dtype=torch.float32, device=dev)
+    for name, o, n in (("nll_out", nll, plan.B), ("loss_sum_out", loss_sum, 1)):
+        if o.dtype != torch.float32 or o.device != dev or o.numel() != n or not o.is_contiguous():
+            raise ValueError(f"{name} must be a contiguous fp32 tensor of {n} element(s) on {dev}")
     grad = grad_out if grad_out is not None else _empty_like_strided(logits)
     gw = None if grad_weight is None else grad_weight.to(device=dev, dtype=torch.float32).contiguous()
     with torch.cuda.device(dev):

@@ -81,3 +81,52 @@ def test_allreduce_without_process_group_is_local():
 
     mean, n = allreduce_loss(torch.tensor(12.0), 4)
     assert float(mean) == 3.0 and float(n) == 4.0
+
+
+def _ledger_worker(rank, world, port, q):
+    from espnet_b200.sharding import LossLedger
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    n_utt = 3 + rank                                   # ragged blocks: 3 and 4 utterances
+    led = LossLedger(4, n_utt, torch.device("cpu"))
+    out = []
+    for rnd in range(2):                               # the ledger is reusable after reduce()
+        for i in range(4):
+            led.slot(4 * rnd + i).fill_(float((rank + 1) * (i + 1) + rnd))
+        means, n = led.reduce()
+        out.append((means.tolist(), float(n)))
+    q.put((rank, out))
+    dist.destroy_process_group()
+
+
+def test_ledger_exchanges_an_interval_of_steps_in_one_allreduce():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_ledger_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, out in res:
+        for rnd, (means, n) in enumerate(out):
+            assert n == 7.0
+            want = [((i + 1) + 2 * (i + 1) + 2 * rnd) / 7.0 for i in range(4)]
+            np.testing.assert_allclose(means, want, rtol=1e-6)
+
+
+def test_ledger_without_process_group_is_local():
+    from espnet_b200.sharding import LossLedger
+
+    led = LossLedger(3, 5, torch.device("cpu"))
+    for i in range(3):
+        led.slot(i).fill_(10.0 * (i + 1))
+    means, n = led.reduce()
+    assert float(n) == 5.0 and means.tolist() == [2.0, 4.0, 6.0]
+    assert led.slot(4).data_ptr() == led.slot(1).data_ptr()
+    with pytest.raises(ValueError):
+        LossLedger(0, 1, torch.device("cpu"))
