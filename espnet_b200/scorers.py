@@ -20,8 +20,20 @@ class _Survivor(object):
 
     def __init__(self, step_state, parent, token):
         self.step_state = step_state
-        self.parent = int(parent)
-        self.token = int(token)
+        self.parent = parent  # int, or a 0-dim device tensor (read only if the hypothesis is scored again)
+        self.token = token
+
+
+class _BeamSurvivors(object):
+    """All survivors of one step, ids still on the device: (state of the step, parent (n,), token (n,))."""
+
+    __slots__ = ("step_state", "parent", "token")
+
+    def __init__(self, step_state, parent, token):
+        self.step_state, self.parent, self.token = step_state, parent, token
+
+    def __len__(self):
+        return self.parent.numel()
 
 
 class CTCPrefixScorer(object):
@@ -47,12 +59,14 @@ class CTCPrefixScorer(object):
 
     def _resolve(self, states):
         """list of per-hypothesis states -> batch state (r_prev, s_prev, f_min, f_max) or None."""
+        if isinstance(states, _BeamSurvivors):
+            return self.impl.select(states.step_state, states.parent, states.token)
         if states[0] is None:
             return None
         step_state = states[0].step_state
         dev = self.impl.device
-        parent = torch.tensor([s.parent for s in states], dtype=torch.int64, device=dev)
-        token = torch.tensor([s.token for s in states], dtype=torch.int64, device=dev)
+        parent = torch.tensor([int(s.parent) for s in states], dtype=torch.int64, device=dev)
+        token = torch.tensor([int(s.token) for s in states], dtype=torch.int64, device=dev)
         return self.impl.select(step_state, parent, token)
 
     # ---- BatchPartialScorerInterface
@@ -67,7 +81,8 @@ class CTCPrefixScorer(object):
         Args:
             y (torch.Tensor): (n_hyps, len) prefix tokens
             ids (torch.Tensor): (n_hyps, snum) next tokens to score, or None for all
-            state: list of per-hypothesis states (from select_state) or [None, ...]
+            state: list of per-hypothesis states (from select_state), [None, ...], or the survivors
+                object of ``batch_select_state``
             x (torch.Tensor): 2D encoder feature that generates ys
         Returns:
             (scores (n_hyps, n_vocab), batch state for select_state)
@@ -75,8 +90,20 @@ class CTCPrefixScorer(object):
         batch_state = self._resolve(state)
         return self.impl(y, batch_state, ids)
 
+    def batch_select_state(self, state, prev_hyp_ids, new_token_ids):
+        """All survivors of a step at once, ids as device tensors (no host round trip): what
+        ``select_state(state, i, new_id)`` does per hypothesis in the reference (scorers/ctc.py:41-64).
+        The result is accepted by ``batch_score_partial`` in place of the list of per-hypothesis states."""
+        return _BeamSurvivors(state, prev_hyp_ids, new_token_ids)
+
+    def batch_keep_state(self, survivors, idx):
+        """Subset (device index tensor) of what ``batch_select_state`` returned."""
+        return _BeamSurvivors(survivors.step_state, survivors.parent[idx], survivors.token[idx])
+
     def select_state(self, state, i, new_id=None):
         """Select state with relative ids in the main beam search (scorers/ctc.py:41-64)."""
+        if isinstance(state, _BeamSurvivors):
+            return _Survivor(state.step_state, state.parent[i], state.token[i])
         if type(state) == tuple:
             if len(state) == 2:  # single-hypothesis path: (scores over ids, (step state, ids))
                 sc, (step_state, ids) = state
@@ -101,3 +128,28 @@ class CTCPrefixScorer(object):
         presub_score = new_state[1][0, ids.to(new_state[1].device)]
         tscore = (presub_score - prev_score).to(device=x.device, dtype=x.dtype)
         return tscore, (presub_score, (new_state, [int(t) for t in ids]))
+
+
+class LengthBonus(object):
+    """Length bonus in beam search: score 1 for every token (espnet/nets/scorers/length_bonus.py:11-61)."""
+
+    def __init__(self, n_vocab: int):
+        self.n = n_vocab
+
+    def init_state(self, x):
+        return None
+
+    def batch_init_state(self, x):
+        return None
+
+    def select_state(self, state, i, new_id=None):
+        return None if state is None else state[i]
+
+    def final_score(self, state):
+        return 0.0
+
+    def score(self, y, state, x):
+        return torch.tensor([1.0], device=x.device, dtype=x.dtype).expand(self.n), None
+
+    def batch_score(self, ys, states, xs):
+        return torch.tensor([1.0], device=xs.device, dtype=xs.dtype).expand(ys.shape[0], self.n), None

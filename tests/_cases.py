@@ -71,3 +71,21 @@ def prefix_cases():
 def viterbi_cases():
     # (T, V, L, seed)
     return [(20, 6, 4, 31), (35, 9, 7, 32), (12, 5, 1, 33)]
+
+
+def nbest_cases():
+    """Beam-search cases: name -> config of tests/_toy.make_search_input and of the search itself."""
+    return {
+        # CTC prefix scores alone (plus the length bonus), every token scored
+        "ctc_only": dict(T=48, V=24, L=9, seed=41, beam=5, weights={"ctc": 1.0, "length_bonus": 0.1},
+                         pre_beam_score_key=None, pre_beam_ratio=1.5, maxlenratio=0.0),
+        # joint decoding: bigram "decoder" 0.7 + CTC 0.3, pre-beam on the full scorers' sum
+        "joint_full": dict(T=60, V=40, L=12, seed=42, beam=6, weights={"decoder": 0.7, "ctc": 0.3, "length_bonus": 0.1},
+                           pre_beam_score_key="full", pre_beam_ratio=1.5, maxlenratio=0.0),
+        # pre-beam on the decoder alone, fixed maximum length (the <eos>-at-the-end branch)
+        "joint_decoder": dict(T=40, V=32, L=8, seed=43, beam=4, weights={"decoder": 0.5, "ctc": 0.5},
+                              pre_beam_score_key="decoder", pre_beam_ratio=2.0, maxlenratio=0.3),
+        # wide beam against a small vocabulary: fewer live candidates than beam slots at step 0
+        "wide_beam": dict(T=30, V=12, L=6, seed=44, beam=10, weights={"ctc": 1.0, "length_bonus": 0.1},
+                          pre_beam_score_key=None, pre_beam_ratio=1.5, maxlenratio=0.0),
+    }

@@ -11,7 +11,8 @@ What is recorded (all from unmodified reference code, CPU, fixed seeds):
                  for a seeded hypothesis walk (full vocabulary and scoring_ids variants),
                  plus the numpy CTCPrefixScore for the first hypothesis.
   viterbi.npz    espnet/nets/pytorch_backend/ctc.py CTC.forced_align.
-  nbest.npz      espnet/nets/batch_beam_search.py BatchBeamSearch n-best with CTCPrefixScorer.
+  nbest.npz      espnet/nets/batch_beam_search.py BatchBeamSearch n-best with CTCPrefixScorer
+                 (separate script: tests/golden/make_golden_nbest.py, also run by --nbest here).
 """
 import os
 import sys

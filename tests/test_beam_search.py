@@ -1,0 +1,108 @@
+"""n-best parity of the batched search against the REFERENCE's BatchBeamSearch n-best lists
+(tests/golden/nbest.npz, made by tests/golden/make_golden_nbest.py): token sequences bit-exact and in the same
+order, scores within 1e-4 per scored token.
+
+CPU tests drive the search glue with the C oracle as the CTC scorer; GPU tests with the product's CUDA scorer."""
+import numpy as np
+import pytest
+import torch
+
+from espnet_b200.batch_beam_search import BatchBeamSearchB200, end_detect
+from espnet_b200.scorers import LengthBonus
+from tests import _cases, _toy
+from tests._util import golden
+
+CASES = sorted(_cases.nbest_cases())
+
+
+def _run(name, ctc_scorer, dev):
+    cfg = _cases.nbest_cases()[name]
+    x, table, _ = _toy.make_search_input(**cfg)
+    V = cfg["V"]
+    scorers = {"decoder": _toy.Bigram(table.to(dev)), "ctc": ctc_scorer, "length_bonus": LengthBonus(V)}
+    bs = BatchBeamSearchB200(scorers=scorers, weights=cfg["weights"], beam_size=cfg["beam"], vocab_size=V,
+                             sos=V - 1, eos=V - 1, pre_beam_score_key=cfg["pre_beam_score_key"],
+                             pre_beam_ratio=cfg["pre_beam_ratio"])
+    with torch.no_grad():
+        return bs(x.to(dev), maxlenratio=cfg["maxlenratio"], minlenratio=0.0), cfg
+
+
+def _check(name, nbest, cfg):
+    g = golden("nbest.npz")
+    ys, score = g[f"{name}_yseq"], g[f"{name}_score"]
+    assert len(nbest) == ys.shape[0]
+    for i, h in enumerate(nbest):
+        want = ys[i][ys[i] >= 0].tolist()
+        assert h.yseq.tolist() == want, f"{name}: hypothesis {i} differs"
+        tol = 1e-4 * len(want)
+        assert abs(float(h.score) - score[i]) <= tol
+        for k in h.scores:
+            assert abs(float(h.scores[k]) - g[f"{name}_scores_{k}"][i]) <= tol
+    # the best hypothesis is the label sequence the input was built around, between sos and eos
+    V = cfg["V"]
+    assert nbest[0].yseq.tolist() == [V - 1] + g[f"{name}_label"].tolist() + [V - 1]
+    assert nbest[0].yseq.tolist() == g[f"{name}_single_best"].tolist()   # and what the non-batch BeamSearch finds
+    d = nbest[0].asdict()
+    assert isinstance(d["yseq"], list) and isinstance(d["score"], float)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_search_glue_with_oracle_scorer_matches_reference_nbest(name):
+    from tests._oracle_scorer import OracleCTCScorer
+
+    nbest, cfg = _run(name, OracleCTCScorer(cfg_eos(name)), torch.device("cpu"))
+    _check(name, nbest, cfg)
+
+
+def cfg_eos(name):
+    return _cases.nbest_cases()[name]["V"] - 1
+
+
+def test_end_detect_rule():
+    assert not end_detect([], 5)
+    # hypotheses of lengths 5, 4, 3 all far below the best: stop
+    ended = [(2, -1.0), (5, -20.0), (4, -21.0), (3, -22.0)]
+    assert end_detect(ended, 5)
+    assert not end_detect(ended, 6)                       # nothing of length 6
+    assert not end_detect([(2, -1.0), (5, -5.0), (4, -21.0), (3, -22.0)], 5)   # length 5 is still competitive
+
+
+def test_scorer_sorting_and_errors():
+    V = 8
+    with pytest.raises(KeyError):
+        BatchBeamSearchB200({"length_bonus": LengthBonus(V)}, {"length_bonus": 1.0}, 2, V, V - 1, V - 1,
+                            pre_beam_score_key="decoder")
+    with pytest.raises(TypeError):
+        BatchBeamSearchB200({"x": object()}, {"x": 1.0}, 2, V, V - 1, V - 1)
+    bs = BatchBeamSearchB200({"length_bonus": LengthBonus(V), "lm": None, "off": LengthBonus(V)},
+                             {"length_bonus": 1.0, "lm": 1.0, "off": 0.0}, 2, V, V - 1, V - 1)
+    assert list(bs.scorers) == ["length_bonus"] and not bs.do_pre_beam
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", CASES)
+def test_b200_scorer_matches_reference_nbest(name):
+    from espnet_b200.scorers import CTCPrefixScorer
+
+    nbest, cfg = _run(name, CTCPrefixScorer(_toy.LogSoftmaxCTC(), cfg_eos(name)), torch.device("cuda"))
+    _check(name, nbest, cfg)
+
+
+class _PerHypothesis(object):
+    """The CUDA scorer behind the reference's per-hypothesis select_state only (no batch_select_state)."""
+
+    def __init__(self, inner):
+        self.inner = inner
+        self.batch_init_state = inner.batch_init_state
+        self.batch_score_partial = inner.batch_score_partial
+        self.select_state = inner.select_state
+
+
+@pytest.mark.gpu
+def test_per_hypothesis_state_path_gives_the_same_nbest():
+    from espnet_b200.scorers import CTCPrefixScorer
+
+    name = "joint_full"
+    nbest, cfg = _run(name, _PerHypothesis(CTCPrefixScorer(_toy.LogSoftmaxCTC(), cfg_eos(name))),
+                      torch.device("cuda"))
+    _check(name, nbest, cfg)
