@@ -1,10 +1,18 @@
 // ctc_loss_occ.inl -- occupancy ("gamma") kernel of the CTC loss (included by ctc_loss.cu).
 //
-// One warp per (utterance, frame) row, rows dealt round-robin to all warps of the grid, every
-// value of a row held in registers (lane j owns the label positions j, j+32, ...).
 // gamma_t(s) ~ 2^(alpha_t(s) + beta_t(s) - lp_t(l'_s)) is normalised over the row (sum_s gamma
 // = 1, so neither the re-centring offsets of the sweeps nor log p(y|x) are needed); states of
 // the same label are merged in label order (deterministic, no atomics).
+//
+// A row of work = frame t of utterance b = three contiguous pieces of the workspace: alpha[b][t]
+// (2L+1 floats), beta[b][t] (2L+1, reversed state order) and lpg[b][t] (L+1).  Every WARP runs its
+// own pipeline: lane 0 brings the three pieces of the next rows into the warp's shared-memory
+// stages with 1-D bulk (TMA) copies that complete on the stage's mbarrier, all lanes reduce the
+// row that has landed (lane j owns label positions j, j+32, ...).  Nothing of a row waits in
+// registers, so the depth of the pipeline is set by shared memory (2-4 rows per warp, 16 warps per
+// SM at L <= 150) and is independent of L: the same code serves L = 1 and L = 1023.
+// The valid rows, in (utterance, frame) order, are cut into equal contiguous ranges, one per warp of the
+// (persistent) grid: a warp streams through its range with the copies `stages` rows ahead of the reduction.
 //
 //   PATCH = false  writes corr[b][t][0..L] = softmax - occupancy of the blank and label columns
 //                  for the separate backward pass (ctc_grad_kernel patches it into the softmax);
@@ -13,200 +21,329 @@
 //                  w * (softmax - occupancy), and whole rows with NaN for infeasible utterances.
 namespace b200 {
 
-constexpr int kOccWarps = 8;
-
 __device__ __forceinline__ uint32_t raw_bits(float v) { return __float_as_uint(v); }
 __device__ __forceinline__ uint32_t raw_bits(__nv_bfloat16 v) { return __bfloat16_as_ushort(v); }
 __device__ __forceinline__ uint32_t raw_bits(__half v) { return __half_as_ushort(v); }
-constexpr int kOccFrames = 4;  // consecutive frames of one utterance per task
 
-template <int NJ>
-struct OccRaw {
-  float a0[NJ], b0[NJ], a1[NJ], b1[NJ], ll[NJ];
-  float lp0;
-};
+constexpr int kOccMaxStages = 4;  // rows in flight per warp
 
-// Work unit = kOccFrames consecutive frames of one utterance, pulled by each WARP from an atomic
-// ticket counter: everything that depends only on the utterance (label columns, duplicate codes,
-// weight) is loaded once per unit, the lattice rows of the unit are double-buffered in registers.
-template <typename T, int NJ, bool PATCH>
-__global__ void __launch_bounds__(kOccWarps * 32, NJ <= 5 ? 2 : 1) ctc_occ_kernel(LossParams p) {
-  __shared__ float s_occ[kOccWarps][NJ * 32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// floats of one stage (alpha row, beta row, lpg row) and of one warp's share of shared memory:
+// stages, un-normalised occupancies [2][Kp], label columns [Kp], 16-bit duplicate codes [Kp]
+__host__ __device__ inline int64_t occ_stage_floats(int64_t Kp) { return 5 * Kp; }
+__host__ __device__ inline int64_t occ_warp_floats(int64_t Kp, int stages) {
+  return stages * occ_stage_floats(Kp) + 3 * Kp + Kp / 2;
+}
+// 16-bit form of LossWs::dupcode (next position + 1 <= 1023)
+constexpr int kDup16Later = 0x8000;
+constexpr int kDup16NextMask = 0x7fff;
+
+// NJ > 0: L + 1 <= 32 * NJ, the row's values stay in registers between the passes (unrolled), and with
+//         four stages TWO rows are reduced together (two independent dependency chains per warp: the
+//         kernel is bound by the latency of one row's ~500 dependent instructions, not by issue slots);
+// NJ = 0: any L, every pass re-reads shared memory, one row at a time.
+template <typename T, bool PATCH, int NJ>
+__global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) {
+  extern __shared__ __align__(128) unsigned char occ_smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int64_t Kp = p.ws.Kp, Sp = p.ws.Sp;
   const int T_ = (int)p.T;
-  const int nblk = (T_ + kOccFrames - 1) / kOccFrames;
-  const int ntask = (p.b1 - p.b0) * nblk;
-  float* occw = s_occ[warp];
+  const int64_t stagef = occ_stage_floats(Kp);
+  float* wbase = reinterpret_cast<float*>(occ_smem) + warp * occ_warp_floats(Kp, stages);
+  float* scratch = wbase + stages * stagef;               // [2][Kp] un-normalised occupancies of the label states
+  int* s_lab = reinterpret_cast<int*>(scratch + 2 * Kp);  // [Kp] label columns of the unit's utterance
+  unsigned short* s_dup = reinterpret_cast<unsigned short*>(s_lab + Kp);  // [Kp] its duplicate codes
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<float*>(occ_smem) + nwarps * occ_warp_floats(Kp, stages)) +
+                   warp * kOccMaxStages;
+  if (lane == 0) {
+    for (int s = 0; s < stages; ++s) mbar_init(&bars[s], 1);
+    mbar_fence_init();
+    fence_proxy_async();
+  }
+  __syncwarp();
+  uint32_t phase = 0;  // bit s: parity of the next completion of stage s
   T* grad = reinterpret_cast<T*>(p.grad);
-  int* counter = p.ws.bad + 3;
+  const bool pairs = NJ > 0 && stages == kOccMaxStages;
+
+  // ---- this warp's share: a contiguous range [r0, r1) of the valid rows, in (utterance, frame) order.
+  // Lengths are inputs of the call, so this runs before the wait on the sweeps.
+  const int nb = p.b1 - p.b0;
+  auto frames_of = [&](int i) { return i < nb ? max(min((int)p.ilen[p.b0 + i], T_), 0) : 0; };
+  int tot = 0;
+  for (int base = 0; base < nb; base += 32) tot += frames_of(base + lane);
+  tot = __reduce_add_sync(0xffffffffu, tot);
+  const int total_warps = gridDim.x * nwarps;
+  const int chunk = (tot + total_warps - 1) / total_warps;
+  const int r0 = min((blockIdx.x * nwarps + warp) * chunk, tot);
+  const int n = min(r0 + chunk, tot) - r0;
+  if (n <= 0) return;
+  // producer cursor (lane 0 issues copies `stages` rows ahead) and consumer cursor, both warp-uniform
+  int pb = 0, pt = 0, pTb = 0, pL = 0;
+  {
+    int run = 0;
+    for (int base = 0; base < nb; base += 32) {
+      const int v = frames_of(base + lane);
+      int incl = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += u;
+      }
+      const int excl = run + incl - v;
+      const unsigned hit = __ballot_sync(0xffffffffu, v > 0 && r0 >= excl && r0 < excl + v);
+      if (hit) {
+        const int src = __ffs(hit) - 1;
+        pb = p.b0 + base + src;
+        pt = r0 - __shfl_sync(0xffffffffu, excl, src);
+        pTb = __shfl_sync(0xffffffffu, v, src);
+        break;
+      }
+      run += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    pL = (int)p.olen[pb];
+  }
+  int b = pb, t = pt, Tb = pTb, L = pL;  // consumer
+  float wgt = 1.f;
+  bool poison = false;
+  // next utterance with frames (there is one whenever this is called: the range has rows left)
+  auto next_utt = [&](int& ub, int& uTb, int& uL) {
+    do {
+      ++ub;
+      uTb = max(min((int)p.ilen[ub], T_), 0);
+    } while (uTb == 0);
+    uL = (int)p.olen[ub];
+  };
   pdl_wait();  // staged under the sweeps: their lattices (and the streamed gradient) are complete from here
 
-  // issue every global load of row (b, t) (nothing waits on them here)
-  auto issue = [&](int b, int t, int L, OccRaw<NJ>& w) {
-    const int64_t row = (int64_t)b * T_ + t;
-    const float* A = p.ws.lat + row * Sp;
-    const float* Bt = p.ws.lat + ((int64_t)p.B * T_ + row) * Sp;
-    const float* lp = p.ws.lpg + row * Kp;
-    w.lp0 = ld_nc_f32(lp);
-#pragma unroll
-    for (int j = 0; j < NJ; ++j) {
-      const int k = lane + 32 * j;
-      const int kb = min(k, L);              // clamped: a valid blank state
-      const int kl = min(k, max(L - 1, 0));  // clamped: a valid label state (if L > 0)
-      w.a0[j] = ld_nc_f32(A + 2 * kb);
-      w.b0[j] = ld_nc_f32(Bt + 2 * (L - kb));
-      w.a1[j] = 0.f; w.b1[j] = 0.f; w.ll[j] = 0.f;
-      if (L > 0) {
-        w.a1[j] = ld_nc_f32(A + 2 * kl + 1);
-        w.b1[j] = ld_nc_f32(Bt + 2 * (L - kl) - 1);
-        w.ll[j] = ld_nc_f32(lp + 1 + kl);
-      }
-    }
-  };
-
-  int q = fetch_ticket(counter, lane);
-  while (q < ntask) {
-    const int b = p.b0 + q / nblk;
-    const int t0 = (q % nblk) * kOccFrames;
-    q = fetch_ticket(counter, lane);  // next ticket: its latency hides behind this unit
-    const int Tb = min((int)p.ilen[b], T_);
-    if (t0 >= Tb) continue;
-    const int t1 = min(t0 + kOccFrames, Tb);
-    const int L = (int)p.olen[b];
-    const int* lab = p.ws.labels + (int64_t)b * Kp;
-    const int* dup = p.ws.dupcode + (int64_t)b * Kp;
-    float wgt = 1.f;
-    bool poison = false;
+  // utterance-level state of the consumer: weight, label columns and duplicate codes
+  auto enter = [&]() {
     if (PATCH) {
       wgt = p.grad_scale * (p.grad_weight ? p.grad_weight[b] : 1.0f);
       poison = isinf(p.ws.nll_ws[b]) || isnan(wgt);
     }
-    int col[NJ], dc[NJ];
-    int anydup = 0;
-#pragma unroll
-    for (int j = 0; j < NJ; ++j) {
-      const int k = lane + 32 * j;
-      col[j] = 0; dc[j] = 0;
-      if (k < L) { col[j] = lab[k]; dc[j] = dup[k]; }
-      anydup |= dc[j];
+    const int* lab = p.ws.labels + (int64_t)b * Kp;
+    const int* dup = p.ws.dupcode + (int64_t)b * Kp;
+    for (int k = lane; k < L; k += 32) {
+      const int dc = dup[k];
+      s_lab[k] = lab[k];
+      s_dup[k] = (unsigned short)((dc & kDupNextMask) | ((dc & kDupLater) ? kDup16Later : 0));
     }
-    const bool merge = __any_sync(0xffffffffu, anydup != 0);
+    __syncwarp();
+  };
+  // copies of the producer's current row into stage s, then the cursor moves on
+  int issued = 0;
+  auto issue = [&](int s) {
+    if (lane == 0) {
+      const uint32_t nA = (uint32_t)(((2 * pL + 1) * 4 + 15) & ~15);  // bytes of a lattice row that are used
+      const uint32_t nL = (uint32_t)(((pL + 1) * 4 + 15) & ~15);
+      const int64_t row = (int64_t)pb * T_ + pt;
+      float* st = wbase + s * stagef;
+      mbar_arrive_expect_tx(&bars[s], 2 * nA + nL);
+      bulk_g2s(st, p.ws.lat + row * Sp, nA, &bars[s]);
+      bulk_g2s(st + Sp, p.ws.lat + ((int64_t)p.B * T_ + row) * Sp, nA, &bars[s]);
+      bulk_g2s(st + 2 * Sp, p.ws.lpg + row * Kp, nL, &bars[s]);
+    }
+    ++issued;
+    if (++pt == pTb && issued < n) { next_utt(pb, pTb, pL); pt = 0; }
+  };
+  for (int i = 0; i < min(stages, n); ++i) issue(i);
+  enter();
 
-    auto process = [&](int t, const OccRaw<NJ>& w) {
-      const int64_t row = (int64_t)b * T_ + t;
-      if (PATCH && poison) {
-        // infeasible utterance: every gradient element of its frames is NaN (as torch)
-        T* dst = grad + (int64_t)b * p.gstride_b + (int64_t)t * p.gstride_t;
-        const T nanv = ElemTraits<T>::from_float(__int_as_float(0x7fc00000));
-        for (int v = lane; v < (int)p.V; v += 32) dst[v] = nanv;
+  {
+    // un-normalised log2 occupancy of the blank state k (k <= L) and of the label state k (k < L)
+    auto logocc = [&](const float* st, int k, float& ub, float& ul) {
+      const float2 a = *reinterpret_cast<const float2*>(st + 2 * k);
+      ub = a.x + st[Sp + 2 * (L - k)] - st[2 * Sp];
+      ul = -3.0e38f;
+      if (k < L) ul = a.y + st[Sp + 2 * (L - k) - 1] - st[2 * Sp + 1 + k];
+    };
+    // blank column of row t, then the label columns through emit()
+    auto emit_blank = [&](int t, const float* st, float w_blank, float inv) {
+      if (lane == 0) {
+        const float g0 = ex2f(st[2 * Sp]) - w_blank * inv;
+        if (PATCH) grad[(int64_t)b * p.gstride_b + (int64_t)t * p.gstride_t + p.blank] = ElemTraits<T>::from_float(wgt * g0);
+        else p.ws.occ[((int64_t)b * T_ + t) * Kp] = g0;
+      }
+    };
+    auto emit = [&](int t, const float* st, const float* scr, float inv, int k) {
+      const int dc = s_dup[k];
+      float* out = p.ws.occ + ((int64_t)b * T_ + t) * Kp;
+      if (dc & kDup16Later) {  // merged into the first occurrence of its label
+        if (!PATCH) out[1 + k] = kCorrSkip;
         return;
       }
-      const float lp0 = w.lp0;
-      float ub[NJ], ul[NJ];
-      float m = -3.0e38f;
+      float o = scr[k];
+      int nx = (dc & kDup16NextMask) - 1;
+      while (nx >= 0) {  // later occurrences of the same label, in label order
+        o += scr[nx];
+        nx = (s_dup[nx] & kDup16NextMask) - 1;
+      }
+      const float pk = ex2f(st[2 * Sp + 1 + k]);
+      if (PATCH) {
+        // The column already holds w * softmax from the stream kernel.  Where the occupancy is too
+        // small to change that value in the output type (most (frame, label) pairs: the occupancy
+        // is concentrated around the alignment), nothing is written: every 2-byte store here costs
+        // a 32-byte sector fill and write-back in DRAM.
+        const T with = ElemTraits<T>::from_float(wgt * (pk - o * inv));
+        const T without = ElemTraits<T>::from_float(wgt * pk);
+        if (raw_bits(with) != raw_bits(without) && !(p.debug & 16))
+          grad[(int64_t)b * p.gstride_b + (int64_t)t * p.gstride_t + s_lab[k]] = with;
+      } else {
+        out[1 + k] = pk - o * inv;
+      }
+    };
+
+    // RR rows (frames t, t+1, ...) in stages st[0..RR), everything unrolled so that the chains interleave
+    auto process_regs = [&](auto rr_tag, int t, const float* const* st) {
+      constexpr int RR = decltype(rr_tag)::value;
+      constexpr int N = NJ > 0 ? NJ : 1;
+      float ub[RR][N], ul[RR][N], m[RR], w_all[RR], w_blank[RR], inv[RR];
 #pragma unroll
-      for (int j = 0; j < NJ; ++j) {
-        const int k = lane + 32 * j;
-        ub[j] = (k <= L) ? (w.a0[j] + w.b0[j] - lp0) : -3.0e38f;
-        ul[j] = (k < L) ? (w.a1[j] + w.b1[j] - w.ll[j]) : -3.0e38f;
-        m = fmaxf(m, fmaxf(ub[j], ul[j]));
+      for (int x = 0; x < RR; ++x) {
+        m[x] = -3.0e38f;
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const int k = lane + 32 * j;
+          ub[x][j] = -3.0e38f; ul[x][j] = -3.0e38f;
+          if (k <= L) logocc(st[x], k, ub[x][j], ul[x][j]);
+          m[x] = fmaxf(m[x], fmaxf(ub[x][j], ul[x][j]));
+        }
+      }
+#pragma unroll
+      for (int x = 0; x < RR; ++x) m[x] = warp_max(m[x]);
+#pragma unroll
+      for (int x = 0; x < RR; ++x) {
+        w_all[x] = 0.f; w_blank[x] = 0.f;
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const int k = lane + 32 * j;
+          ub[x][j] = ex2f(ub[x][j] - m[x]);  // -3e38 - m underflows to 0
+          ul[x][j] = ex2f(ul[x][j] - m[x]);
+          w_blank[x] += ub[x][j];
+          w_all[x] += ul[x][j];
+          if (k <= L) scratch[x * Kp + k] = ul[x][j];
+        }
+      }
+#pragma unroll
+      for (int x = 0; x < RR; ++x) {
+        w_all[x] = warp_sum(w_all[x] + w_blank[x]);
+        w_blank[x] = warp_sum(w_blank[x]);
+        inv[x] = 1.0f / w_all[x];
+      }
+      __syncwarp();  // scratch complete
+#pragma unroll
+      for (int x = 0; x < RR; ++x) {
+        emit_blank(t + x, st[x], w_blank[x], inv[x]);
+#pragma unroll
+        for (int j = 0; j < N; ++j)
+          if (lane + 32 * j < L) emit(t + x, st[x], scratch + x * Kp, inv[x], lane + 32 * j);
+      }
+    };
+    auto process_loop = [&](int t, const float* st) {
+      float m = -3.0e38f, w_all = 0.f, w_blank = 0.f;
+      for (int k = lane; k <= L; k += 32) {
+        float ub, ul;
+        logocc(st, k, ub, ul);
+        m = fmaxf(m, fmaxf(ub, ul));
       }
       m = warp_max(m);
-      float w_all = 0.f, w_blank = 0.f;
-#pragma unroll
-      for (int j = 0; j < NJ; ++j) {
-        ub[j] = ex2f(ub[j] - m);  // -3e38 - m underflows to 0
-        ul[j] = ex2f(ul[j] - m);
-        w_blank += ub[j];
-        w_all += ul[j];
+      for (int k = lane; k <= L; k += 32) {
+        float ub, ul;
+        logocc(st, k, ub, ul);
+        ub = ex2f(ub - m);
+        ul = ex2f(ul - m);
+        w_blank += ub;
+        w_all += ul;
+        scratch[k] = ul;
       }
       w_all = warp_sum(w_all + w_blank);
       w_blank = warp_sum(w_blank);
       const float inv = 1.0f / w_all;
-      if (merge) {
-        // merge the occupancies of repeated labels into their first occurrence, in label order
-        __syncwarp();
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) occw[lane + 32 * j] = ul[j];
-        __syncwarp();
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) {
-          if (dc[j] > 0 && !(dc[j] & kDupLater)) {
-            float o = ul[j];
-            int nx = (dc[j] & kDupNextMask) - 1;
-            while (nx >= 0) {
-              o += occw[nx];
-              nx = (dup[nx] & kDupNextMask) - 1;
-            }
-            ul[j] = o;
-          }
-        }
-      }
-      if (PATCH && (p.debug & 16)) {
-        if (w_blank * inv == 123.f) p.ws.occ[row] = inv;  // developer variant: no scattered stores
-      } else if (PATCH) {
-        T* dst = grad + (int64_t)b * p.gstride_b + (int64_t)t * p.gstride_t;
-        if (lane == 0) dst[p.blank] = ElemTraits<T>::from_float(wgt * (ex2f(lp0) - w_blank * inv));
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) {
-          const int k = lane + 32 * j;
-          if (k < L && !(dc[j] & kDupLater)) {
-            // The column already holds w * softmax from the stream kernel.  Where the occupancy is
-            // too small to change that value in the output type (most (frame, label) pairs: the
-            // occupancy is concentrated around the alignment), nothing is written: every 2-byte
-            // store here costs a 32-byte sector fill and write-back in DRAM.
-            const float pk = ex2f(w.ll[j]);
-            const T with = ElemTraits<T>::from_float(wgt * (pk - ul[j] * inv));
-            const T without = ElemTraits<T>::from_float(wgt * pk);
-            if (raw_bits(with) != raw_bits(without)) dst[col[j]] = with;
-          }
-        }
-      } else {
-        float* out = p.ws.occ + row * Kp;
-        if (lane == 0) out[0] = ex2f(lp0) - w_blank * inv;
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) {
-          const int k = lane + 32 * j;
-          if (k < L) out[1 + k] = (dc[j] & kDupLater) ? kCorrSkip : ex2f(w.ll[j]) - ul[j] * inv;
-        }
-      }
+      __syncwarp();  // scratch complete
+      emit_blank(t, st, w_blank, inv);
+      for (int k = lane; k < L; k += 32) emit(t, st, scratch, inv, k);
     };
 
-    // two register sets: the loads of the next row are in flight while this row is reduced and stored
-    OccRaw<NJ> ra, rb;
-    issue(b, t0, L, ra);
-    for (int t = t0; t < t1; t += 2) {
-      if (t + 1 < t1) issue(b, t + 1, L, rb);
-      process(t, ra);
-      if (t + 1 >= t1) break;
-      if (t + 2 < t1) issue(b, t + 2, L, ra);
-      process(t + 1, rb);
+    for (int r = 0; r < n;) {
+      const int s = r % stages;
+      const int cnt = (pairs && r + 1 < n && t + 1 < Tb) ? 2 : 1;  // two frames of the same utterance
+      const float* st[2] = {wbase + s * stagef, wbase + ((s + 1) % stages) * stagef};
+      for (int i = 0; i < cnt; ++i) {
+        const int si = (s + i) % stages;
+        mbar_wait(&bars[si], (phase >> si) & 1u);
+        phase ^= 1u << si;
+      }
+      if (PATCH && poison) {
+        // infeasible utterance: every gradient element of its frames is NaN (as torch)
+        const T nanv = ElemTraits<T>::from_float(__int_as_float(0x7fc00000));
+        for (int x = 0; x < cnt; ++x) {
+          T* dst = grad + (int64_t)b * p.gstride_b + (int64_t)(t + x) * p.gstride_t;
+          for (int v = lane; v < (int)p.V; v += 32) dst[v] = nanv;
+        }
+      } else if (p.debug & 32) {
+      } else if constexpr (NJ > 0) {
+        if (cnt == 2) process_regs(std::integral_constant<int, 2>{}, t, st);
+        else process_regs(std::integral_constant<int, 1>{}, t, st);
+      } else {
+        process_loop(t, st[0]);
+      }
+      __syncwarp();  // every lane is done with the stages (and with scratch) before they are refilled
+      for (int i = 0; i < cnt; ++i)
+        if (issued < n) issue((s + i) % stages);
+      r += cnt;
+      t += cnt;
+      if (t == Tb && r < n) {
+        next_utt(b, Tb, L);
+        t = 0;
+        enter();
+      }
     }
   }
 }
 
-template <typename T, int NJ, bool PATCH>
+struct OccPlan {
+  int warps, stages;
+  size_t smem;
+};
+
+// Largest pipeline that fits: 8 warps x up to 4 stages with two CTAs per SM if the rows are short,
+// fewer warps / stages and one CTA per SM for long label sequences (a row is 20 * Kp bytes).
+static OccPlan plan_occ(int64_t Kp) {
+  const size_t budgets[2] = {112u * 1024u, (size_t)max_smem_optin() - 1024u};
+  for (size_t budget : budgets) {
+    for (int warps = 8; warps >= 1; warps >>= 1) {
+      for (int stages = kOccMaxStages; stages >= 2; --stages) {
+        const size_t smem = (size_t)warps * ((size_t)occ_warp_floats(Kp, stages) * 4 + kOccMaxStages * 8);
+        if (smem <= budget) return OccPlan{warps, stages, smem};
+      }
+    }
+  }
+  return OccPlan{0, 0, 0};
+}
+
+template <typename T, bool PATCH, int NJ>
 static int launch_occ_nj(const LossParams& p, cudaStream_t st) {
-  const int64_t nrows = ((int64_t)(p.b1 - p.b0) * ((p.T + kOccFrames - 1) / kOccFrames));  // tasks
+  const OccPlan pl = plan_occ(p.ws.Kp);
+  B200_CHECK_ARG(pl.warps > 0, B200_ERR_UNSUPPORTED_SHAPE, "Lmax=%lld: a lattice row does not fit in shared memory",
+                 (long long)p.Lmax);
+  B200_CUDA(cudaFuncSetAttribute(ctc_occ_kernel<T, PATCH, NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+  const int64_t units = (int64_t)(p.b1 - p.b0) * p.T;  // rows, at least one per warp
   int per_sm = 1;
-  B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ctc_occ_kernel<T, NJ, PATCH>, kOccWarps * 32, 0));
+  B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ctc_occ_kernel<T, PATCH, NJ>, pl.warps * 32, pl.smem));
   if (per_sm < 1) per_sm = 1;
-  int64_t g = (nrows + kOccWarps - 1) / kOccWarps;
+  int64_t g = (units + pl.warps - 1) / pl.warps;
   const int64_t cap = (int64_t)num_sms() * per_sm;  // persistent: every CTA resident
   if (g > cap) g = cap;
   if (g < 1) g = 1;
-  B200_CUDA(launch_kernel(ctc_occ_kernel<T, NJ, PATCH>, dim3((unsigned)g), dim3(kOccWarps * 32), 0, st, PATCH, p));
+  B200_CUDA(launch_kernel(ctc_occ_kernel<T, PATCH, NJ>, dim3((unsigned)g), dim3(pl.warps * 32), pl.smem, st, PATCH, p,
+                          pl.stages));
   return B200_OK;
 }
 
 template <typename T, bool PATCH>
 static int launch_occ_t(const LossParams& p, cudaStream_t st) {
-  const int nj = (int)((p.Lmax + 1 + 31) / 32);
-  if (nj <= 5) return launch_occ_nj<T, 5, PATCH>(p, st);
-  if (nj <= 10) return launch_occ_nj<T, 10, PATCH>(p, st);
-  if (nj <= 20) return launch_occ_nj<T, 20, PATCH>(p, st);
-  return launch_occ_nj<T, 32, PATCH>(p, st);
+  if (p.Lmax + 1 <= 32 * 5) return launch_occ_nj<T, PATCH, 5>(p, st);
+  if (p.Lmax + 1 <= 32 * 10) return launch_occ_nj<T, PATCH, 10>(p, st);
+  return launch_occ_nj<T, PATCH, 0>(p, st);
 }
 
 // occupancies into ws.occ (separate forward / backward calls)

@@ -328,6 +328,243 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
   if (p.wait_rows) pdl_wait();
 }
 
+// ------------------------------------------------------------------------------------------------
+// The same recursion for L <= 255 with the log-prob rows of every full chunk STAGED IN SHARED MEMORY:
+// thread 0 brings the CHF rows of a chunk (contiguous in lpg) in with one 1-D bulk (TMA) copy, kLpAhead
+// chunks before warp 0 needs them, into a ring of kLpSlots chunks; every warp waits on the slot's
+// mbarrier and reads its blank / label columns with LDS.  In the register-prefetch kernel above two
+// thirds of the per-chunk instructions were 64-bit address arithmetic for 16 global loads, executed
+// serially by each (latency-bound) warp; here a chunk costs 16 LDS with uniform-register addressing.
+// Slot reuse needs no "empty" barrier: warp 0 passes chunk c only after every warp has published its
+// level of chunk c - delay_p (chunk_begin), i.e. has finished reading all earlier chunks, and
+// kLpSlots > delay_p + kLpAhead + 2.
+constexpr int kLpSlots = 16;
+constexpr int kLpAhead = 3;
+
+__global__ void __launch_bounds__(256) ctc_sweep_staged_kernel(LossParams p) {
+  constexpr int CHF = 8, MAXT = 256;
+  static_assert(kLpSlots > MAXT / 32 + kLpAhead + 3, "lp ring");
+  extern __shared__ __align__(16) unsigned char sw_smem[];
+  constexpr int kR = SweepRings<MAXT>::kR, kWR = SweepRings<MAXT>::kWR;
+  static_assert(CHF == SweepRings<MAXT>::kCHF, "chunk size");
+  pdl_launch_dependents();  // the occupancy kernel may be staged; it waits for this grid to finish
+  const int b = p.ws.order[p.b0 + blockIdx.x];
+  const int d = blockIdx.y;
+  const int Tb = min((int)p.ilen[b], (int)p.T);
+  const int L = (int)p.olen[b];
+  const int i = threadIdx.x;
+  const int lane = i & 31, warp = i >> 5;
+  const int nw = blockDim.x >> 5;
+  const int Kp = (int)p.ws.Kp;
+  const int64_t Sp = p.ws.Sp;
+  const int nwa = L / 32 + 1;  // warps that own at least one state (threads 0..L)
+  Tagged* s_bnd = reinterpret_cast<Tagged*>(sw_smem);  // [nw][kR] label state of lane 31 of warp w at frame f
+  Tagged* s_wmx = s_bnd + (size_t)nw * kR;             // [kWR][nw] maximum over the states of warp w at the start of chunk c
+  int* s_hist = reinterpret_cast<int*>(s_wmx + (size_t)kWR * nw);  // [kWR] total removed before chunk c
+  const int slot_floats = CHF * Kp;
+  float* s_lp = reinterpret_cast<float*>(s_hist + kWR);  // [kLpSlots][CHF][Kp] rows of lpg, chunk c >= 1 in slot (c - 1) % kLpSlots
+  uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_lp + (size_t)kLpSlots * slot_floats);
+  __shared__ float s_fin[2];
+
+  if (Tb <= 0) {
+    if (i == 0) {
+      if (d == 0) sweep_finish_nll(p, b, (L == 0) ? 0.0f : __int_as_float(0x7f800000));
+      else p.ws.logz_beta[b] = (L == 0) ? 0.0f : B200_NEG;
+    }
+    pdl_wait();
+    return;
+  }
+  for (int k = i; k < nw * kR + kWR * nw; k += blockDim.x) s_bnd[k].tag = -1;
+  if (i == 0) {
+    for (int k = 0; k < kLpSlots; ++k) mbar_init(&s_bar[k], 1);
+    mbar_fence_init();
+    fence_proxy_async();
+  }
+  const int nfull = Tb / CHF;  // chunks 1 .. nfull-1 are full and take the fast path
+  const float* lpg_b = p.ws.lpg + (int64_t)b * p.T * Kp;
+  // rows of chunk c (logical frames c*CHF ..): physical rows c*CHF.. (alpha) or Tb-1-c*CHF-(CHF-1).. (beta)
+  auto stage = [&](int c) {
+    const int slot = (c - 1) % kLpSlots;
+    const int prow = d ? (Tb - 1 - c * CHF - (CHF - 1)) : c * CHF;
+    mbar_arrive_expect_tx(&s_bar[slot], (uint32_t)(slot_floats * 4));
+    bulk_g2s(s_lp + (size_t)slot * slot_floats, lpg_b + (int64_t)prow * Kp, (uint32_t)(slot_floats * 4), &s_bar[slot]);
+  };
+  pdl_wait();  // staged under the kernel that produces lpg: it is complete from here
+  __syncthreads();
+  if (warp >= nwa) return;
+  if (i == 0)
+    for (int c = 1; c <= kLpAhead && c < nfull; ++c) stage(c);
+
+  const int* lab = p.ws.labels + (int64_t)b * Kp;
+  const bool has_label = i < L;
+  const bool active = i <= L;
+  const int pi = d ? (L - 1 - i) : i;  // physical label position of logical position i
+  bool skip_ok = false;
+  if (has_label && i >= 1) skip_ok = lab[pi] != lab[d ? pi + 1 : pi - 1];
+  const float skipmask = skip_ok ? 0.0f : B200_NEG;
+  const int kcol = has_label ? 1 + pi : 0;
+  // logical frame f is physical frame f (alpha) or Tb-1-f (beta): rows of lpg and of the lattice
+  const float* lp0 = p.ws.lpg + ((int64_t)b * p.T + (d ? (Tb - 1) : 0)) * Kp;
+  const int lstep = d ? -Kp : Kp;
+  float* outp = p.ws.lat + (((int64_t)d * p.B + b) * p.T + (d ? (Tb - 1) : 0)) * Sp + 2 * i;
+  const int64_t ostep = d ? -Sp : Sp;
+  const bool lane0 = lane == 0, lane31 = lane == 31;
+  const bool poll = warp > 0;
+  const Tagged* bsrc = s_bnd + (size_t)(poll ? warp - 1 : 0) * kR;
+  Tagged* bdst = s_bnd + (size_t)warp * kR;
+  // the most skewed warp publishes its level of chunk m when warp 0 is around chunk m + nwa - 1
+  const int delay = nwa;
+
+  float ab = B200_NEG, al = B200_NEG;
+  float dstep = 0.f;
+  int csum = 0;                      // exact sum of everything removed so far
+  float xprev = 0.f; int sprev = 0;  // previous consumed level measurement and its csum
+  bool have_prev = false;
+
+  // one frame of the recursion; bn = label state of the last lane of the previous warp at the previous frame
+  auto frame = [&](float lb_t, float ll_t, float bn, float o, int fr) {
+    const float sh = __shfl_up_sync(0xffffffffu, al, 1);
+    const float nbr = lane0 ? bn : sh;
+    const float hi = fmaxf(al, ab);
+    const float s1 = 1.0f + ex2f(-fabsf(al - ab));
+    const float x = lse2_abs(ab, nbr);
+    const float y = lse3_pre(hi, s1, nbr + skipmask);
+    ab = (lb_t - o) + x;
+    al = (ll_t - o) + y;
+    if (lane31) sts_tagged(&bdst[fr & (kR - 1)], al, fr);
+    if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
+    outp += ostep;
+  };
+  // start of chunk c >= 1 (n frames): publish this warp's level, consume everybody's of chunk
+  // c - delay, derive the integer removals of this chunk (dstep per frame, corr once)
+  auto chunk_begin = [&](int c, int n) -> float {
+    // levels are published and consumed every kP-th chunk only (this is per-chunk overhead on the
+    // critical path of every warp); dstep holds in between
+    constexpr int kP = 2;
+    if (c % kP) return 0.f;
+    float corr = 0.f;
+    const float wm = warp_max_redux(fmaxf(ab, al));
+    if (lane31) {
+      sts_tagged(&s_wmx[(c & (kWR - 1)) * nw + warp], wm, c);
+      s_hist[c & (kWR - 1)] = csum;
+    }
+    __syncwarp();
+    const int delay_p = (delay + kP - 1) / kP * kP;
+    const int cm = c - delay_p;
+    if (cm >= kP) {
+      Tagged e;
+      e.v = B200_NEG; e.tag = cm;
+      if (lane < nwa) {
+        const Tagged* src = &s_wmx[(cm & (kWR - 1)) * nw + lane];
+        do { e = lds_tagged(src); } while (e.tag != cm);
+      }
+      __syncwarp();
+      const float xm = warp_max_redux(e.v);
+      const int sm = s_hist[cm & (kWR - 1)];
+      // uncentred level y = x + S; drift per frame from two consecutive measurements
+      float delta = dstep;
+      if (have_prev) delta = (xm - xprev + (float)(sm - sprev)) * (1.0f / (kP * CHF));
+      xprev = xm; sprev = sm; have_prev = true;
+      const float xhat = xm + (float)(sm - csum) + delta * (float)(CHF * delay_p);  // level now
+      // remove, over the next kP chunks, what brings the level back to zero at their end
+      const float horizon = (float)(n == CHF ? kP * CHF : n);
+      dstep = clamp_int_f(delta);
+      corr = clamp_int_f(clamp_int_f(xhat + delta * horizon) - dstep * horizon);
+    }
+    return corr;
+  };
+  // generic (slow) chunk: the first chunk and a trailing partial chunk; reads lpg directly
+  auto slow_chunk = [&](int c, int n) {
+    const int f0 = c * CHF;
+    float corr = 0.f;
+    if (c == 0) {
+      if (Tb > 1) dstep = clamp_int_f(floorf(ld_relaxed_f32(lp0 + lstep)));
+      if (lane31) s_hist[0] = 0;
+    } else {
+      corr = chunk_begin(c, n);
+    }
+    // all loads of the chunk first (one memory latency, not one per frame)
+    float sb[CHF], sl[CHF];
+#pragma unroll
+    for (int f = 0; f < CHF; ++f) {
+      const float* rowp = lp0 + (int64_t)(f0 + min(f, n - 1)) * lstep;
+      sb[f] = ld_relaxed_f32(rowp);
+      sl[f] = has_label ? ld_relaxed_f32(rowp + kcol) : B200_NEG;
+    }
+#pragma unroll
+    for (int f = 0; f < CHF; ++f) {
+      if (f < n) {
+        const int fr = f0 + f;
+        const float lb_t = sb[f], ll_t = sl[f];
+        if (fr == 0) {
+          // frame 0: only the first blank and the first label are reachable
+          if (i == 0) { ab = lb_t; al = ll_t; }
+          if (lane31) sts_tagged(&bdst[0], al, 0);
+          if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
+          outp += ostep;
+        } else {
+          Tagged e;
+          e.v = B200_NEG; e.tag = fr - 1;
+          if (poll) {
+            do { e = lds_tagged(&bsrc[(fr - 1) & (kR - 1)]); } while (e.tag != fr - 1);
+          }
+          frame(lb_t, ll_t, e.v, dstep + (f == 0 ? corr : 0.f), fr);
+        }
+      }
+    }
+    csum += (n - (c == 0 ? 1 : 0)) * (int)dstep + (int)corr;
+  };
+  // full chunk c >= 1: straight-line code, no branch inside the frames
+  auto fast_chunk = [&](int c) {
+    const int f0 = c * CHF;
+    if (i == 0 && c + kLpAhead < nfull) stage(c + kLpAhead);
+    const int slot = (c - 1) % kLpSlots;  // chunk 0 is never staged
+    mbar_wait(&s_bar[slot], (uint32_t)(((c - 1) / kLpSlots) & 1));
+    const float* sl = s_lp + (size_t)slot * slot_floats;
+    float xb[CHF], xl[CHF];
+#pragma unroll
+    for (int f = 0; f < CHF; ++f) {
+      const float* row = sl + (d ? (CHF - 1 - f) : f) * Kp;
+      xb[f] = row[0];
+      xl[f] = has_label ? row[kcol] : B200_NEG;  // a missing label state stays at log(0)
+    }
+    const float corr = chunk_begin(c, CHF);
+    float bn[CHF];
+#pragma unroll
+    for (int f = 0; f < CHF; ++f) bn[f] = B200_NEG;
+    if (poll) {
+      // boundary values of frames f0-1 .. f0+CHF-2 from the previous warp.  One lane publishes them in
+      // frame order, so the last record being there means that all of them are.
+      const Tagged* last = &bsrc[(f0 + CHF - 2) & (kR - 1)];
+      Tagged e;
+      do { e = lds_tagged(last); } while (e.tag != f0 + CHF - 2);
+      bn[CHF - 1] = e.v;
+#pragma unroll
+      for (int f = 0; f < CHF - 1; ++f) bn[f] = lds_tagged(&bsrc[(f0 + f - 1) & (kR - 1)]).v;
+    }
+#pragma unroll
+    for (int f = 0; f < CHF; ++f) frame(xb[f], xl[f], bn[f], dstep + (f == 0 ? corr : 0.f), f0 + f);
+    csum += CHF * (int)dstep + (int)corr;
+  };
+
+  slow_chunk(0, min(CHF, Tb));
+  for (int c = 1; c < nfull; ++c) fast_chunk(c);
+  if (nfull >= 1 && Tb > nfull * CHF) slow_chunk(nfull, Tb - nfull * CHF);
+
+  // log2 p(y|x) = lse2(state 2L, state 2L-1) + sum of offsets
+  if (i == L) s_fin[0] = ab;
+  if (L == 0 && i == 0) s_fin[1] = B200_NEG;
+  if (L > 0 && i == L - 1) s_fin[1] = al;
+  asm volatile("bar.sync 1, %0;" ::"r"(nwa * 32) : "memory");
+  if (i == 0) {
+    const float z = lse2(s_fin[0], s_fin[1]);
+    const bool feasible = z > -1.0e29f;
+    const float logz2 = z + (float)csum;
+    if (d == 0) sweep_finish_nll(p, b, feasible ? -B200_LN2 * logz2 : __int_as_float(0x7f800000));
+    else p.ws.logz_beta[b] = feasible ? logz2 : B200_NEG;
+  }
+}
+
 template <int MAXT>
 static size_t sweep_smem_bytes(int nw) {
   const size_t kR = SweepRings<MAXT>::kR, kWR = SweepRings<MAXT>::kWR;
@@ -347,9 +584,20 @@ static int launch_sweep_t(const LossParams& p, int threads, cudaStream_t st, boo
   return B200_OK;
 }
 
-// pdl: staged under the stream kernel of the same call (p.wait_rows must be set)
+static int launch_sweep_staged(const LossParams& p, int threads, cudaStream_t st, bool pdl) {
+  size_t smem = sweep_smem_bytes<256>(threads / 32) + (size_t)kLpSlots * 8 * p.ws.Kp * sizeof(float) + kLpSlots * sizeof(uint64_t);
+  // one latency chain per SM whenever the grid fits that way (see launch_sweep_t)
+  if (2 * (p.b1 - p.b0) <= num_sms() && smem < 116 * 1024) smem = 116 * 1024;
+  auto kern = ctc_sweep_staged_kernel;
+  if (smem > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  B200_CUDA(launch_kernel(kern, dim3((unsigned)(p.b1 - p.b0), 2), dim3(threads), smem, st, pdl, p));
+  return B200_OK;
+}
+
+// pdl: staged under the stream kernel of the same call
 static int launch_sweep(const LossParams& p, cudaStream_t st, bool pdl = false) {
   const int threads = (int)align_up((size_t)(p.Lmax + 1), 32);
+  if (threads <= 256 && !p.wait_rows && !(p.debug & 64)) return launch_sweep_staged(p, threads, st, pdl);
   if (threads <= 256) return launch_sweep_t<8, 256>(p, threads, st, pdl);
   return launch_sweep_t<4, 1024>(p, threads, st, pdl);
 }
