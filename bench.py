@@ -82,6 +82,38 @@ def cpu_reference_pass(batch, n_utt, threads):
     return time.perf_counter() - t0, float(loss.detach())
 
 
+def gpu_reference_pass(batch, dev, steps=10):
+    """SURVEY 8d "reference GPU baseline on the same box": what CTC.loss_fn (espnet2/asr/ctc.py:46-52) executes
+    on a CUDA device -- .float() of the bf16 logits (autocast's promotion), log_softmax(2),
+    torch.nn.CTCLoss(sum) / B, backward to the fp32 logits -- timed with CUDA events.  Stock PyTorch only."""
+    x = batch["x"].to(dev)
+    ilen, olen = batch["ilen"].to(dev), batch["olen"].to(dev)
+    tg = torch.cat([batch["ys"][i, : batch["olen"][i]] for i in range(x.size(0))]).to(dev)
+    crit = torch.nn.CTCLoss(reduction="sum")
+    xt = x.transpose(0, 1)
+
+    def one():
+        xf = xt.float().requires_grad_()
+        loss = crit(xf.log_softmax(2), tg, ilen, olen) / xf.size(1)
+        loss.backward()
+        return loss
+
+    for _ in range(3):
+        one()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss = one()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"value": x.size(0) / (ms * 1e-3), "unit": "utterances/s", "ms_per_step": ms, "steps": steps,
+            "loss": float(loss) , "kind": "stock torch on the same GPU",
+            "what": "bf16 logits .float() -> log_softmax(2) -> torch.nn.CTCLoss(sum)/B -> backward "
+                    "(espnet2/asr/ctc.py:46-52 as it runs under autocast)"}
+
+
 def cpu_oracle_pass(batch, n_utt):
     """The C restatement (oracle/ctc_oracle.c), one utterance per OpenMP thread."""
     import numpy as np
@@ -364,9 +396,17 @@ def run_b200(args, rank, world, local_rank):
             cpu = {"value": n_utt / t_ref, "unit": "utterances/s", "cores": cores, "kind": "port",
                    "sample": f"{n_utt} C2 utterances, torch CPU ctc_loss (oracle build failed: {e})"}
     prefix = None
-    if world == 1 and not args.no_prefix:
+    ref_gpu = None
+    if world == 1:
         del grad
         torch.cuda.empty_cache()
+        try:
+            ref_gpu = gpu_reference_pass(batch, dev)
+            ref_gpu["speedup_device_resident"] = value / ref_gpu["value"]
+        except Exception as e:  # reported baseline only
+            ref_gpu = {"error": str(e)[:200]}
+        torch.cuda.empty_cache()
+    if world == 1 and not args.no_prefix:
         prefix = bench_prefix(dev)
     line = {"metric": "ctc_loss_fwd_bwd_utterances_per_sec", "value": value, "unit": "utterances/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
@@ -374,7 +414,7 @@ def run_b200(args, rank, world, local_rank):
             "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e,
             "gpu_launches": KERNELS_PER_STEP * args.steps,
             "kernels_per_step": ["ctc_prep_kernel", "ctc_stream_kernel", "ctc_sweep_kernel", "ctc_occ_kernel<PATCH>"], "roofline": roofline, "roofline_step": roofline_step,
-            "cpu_baseline": cpu, "loss": loss_value, "prefix": prefix}
+            "cpu_baseline": cpu, "reference_gpu": ref_gpu, "loss": loss_value, "prefix": prefix}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
