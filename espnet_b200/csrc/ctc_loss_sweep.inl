@@ -348,6 +348,13 @@ constexpr int kLpSlots = 16;   // chunks of rows [CHF frames][Kp columns] as the
 constexpr int kLpAhead = 4;    // bulk copies are issued this many chunks ahead of their first reader
 constexpr int kCtlRing = 32;   // control records, in chunks
 
+// (pick ? a : b) - c as two predicated subtractions: the one on `b` does not wait for `a` and vice versa
+__device__ __forceinline__ float sub_pick(bool pick, float a, float b, float c) {
+  float r;
+  asm("{\n.reg .pred p;\nsetp.ne.s32 p, %4, 0;\n@p sub.f32 %0, %1, %3;\n@!p sub.f32 %0, %2, %3;\n}"
+      : "=f"(r) : "f"(a), "f"(b), "f"(c), "r"((int)pick));
+  return r;
+}
 __device__ __forceinline__ float lds_f32(uint32_t a) {
   float v;
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
@@ -528,15 +535,26 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
   float ab = B200_NEG, al = B200_NEG;
 
   // one frame of the recursion; bn = label state of the last lane of the previous warp at the previous frame
+  // (the label state is the critical chain shfl -> sub -> ex2 -> add -> lg2 -> add -> add -> shfl: the skip
+  // mask is folded into the own-state side, hi - skipmask, which is known before the shuffle returns, and
+  // the label state's ex2 / lg2 are issued before the blank state's)
   auto frame = [&](float lb_t, float ll_t, float bn, float o, int fr) {
     const float sh = __shfl_up_sync(0xffffffffu, al, 1);
-    const float nbr = lane0 ? bn : sh;
     const float hi = fmaxf(al, ab);
     const float s1 = 1.0f + ex2f(-fabsf(al - ab));
-    const float x = lse2_abs(ab, nbr);
-    const float y = lse3_pre(hi, s1, nbr + skipmask);
-    ab = (lb_t - o) + x;
-    al = (ll_t - o) + y;
+    const float hi2 = hi - skipmask;  // +1e30 when the skip transition is not allowed: its term vanishes
+    const float lbo = lb_t - o, llo = ll_t - o;
+    // lane 0 takes the boundary value: two predicated subtractions instead of a select in front of one
+    const float dl = sub_pick(lane0, bn, sh, hi2);  // neighbour - hi2
+    const float db = sub_pick(lane0, bn, sh, ab);   // neighbour - ab
+    const float t = ex2f(-fabsf(dl));
+    const float u = ex2f(-fabsf(db));
+    const float nbr = lane0 ? bn : sh;
+    const float sum = (dl <= 0.f) ? (s1 + t) : fmaf(s1, t, 1.0f);
+    const float mxl = llo + (skip_ok ? fmaxf(hi, nbr) : hi);
+    const float mxb = lbo + fmaxf(ab, nbr);
+    al = mxl + lg2f(sum);
+    ab = mxb + lg2f(1.0f + u);
     if (lane31) sts_tagged(&bdst[(fr + 1) & (kR - 1)], al, fr);
     if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
     outp += ostep;
