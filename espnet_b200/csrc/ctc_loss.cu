@@ -16,6 +16,9 @@ __global__ void ctc_prep_kernel(LossParams p) {
   int* nxt = p.ws.dup_next + (int64_t)b * p.ws.Kp;
   int* fst = p.ws.is_first + (int64_t)b * p.ws.Kp;
   extern __shared__ int s_lab[];
+  // the counters of the kernels that follow (task queues, finished-sweep count) start at zero; this grid
+  // completes before any of them runs, so no separate memset node is needed in front of a call
+  if (blockIdx.x == 0 && threadIdx.x >= 1 && threadIdx.x < 8) p.ws.bad[threadIdx.x] = 0;
   for (int64_t i = threadIdx.x; i < L; i += blockDim.x) {
     int64_t v = y[i];
     if (v < 0 || v >= p.V || v == p.blank) {
@@ -64,6 +67,9 @@ __global__ void ctc_prep_kernel(LossParams p) {
     const uint4 nanv = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
     for (int64_t k = threadIdx.x; k < n4; k += blockDim.x) dst[k] = nanv;
   }
+  // launched as a programmatic dependent of the stream kernel: this grid must not be seen as finished
+  // before the kernel it ran under (the sweeps wait for THIS grid only)
+  if (p.prep_after_stream) pdl_wait();
 }
 
 // deterministic sum of the per-utterance nll

@@ -96,6 +96,7 @@ struct LossParams {
                   // every lpg word they need until it is a number (the stream kernel never writes a NaN)
   float* loss_sum; // sum_b nll[b], written by the sweep CTA that finishes last (may be NULL)
   int debug;      // developer experiments (B200_DEBUG_VARIANT), 0 in production
+  int prep_after_stream;  // fused call: the prep kernel is a programmatic dependent of the stream kernel
 };
 
 }  // namespace b200

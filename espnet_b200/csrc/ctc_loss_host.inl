@@ -141,8 +141,8 @@ static int launch_prep(const LossParams& p, cudaStream_t st) {
   int threads = (int)align_up((size_t)(p.Lmax > 0 ? p.Lmax : 1), 32);
   if (threads > 1024) threads = 1024;
   const size_t sm = sizeof(int) * (size_t)(p.Lmax > 0 ? p.Lmax : 1);
-  ctc_prep_kernel<<<(unsigned)(p.b1 - p.b0), threads, sm, st>>>(p);
-  B200_CUDA(cudaGetLastError());
+  B200_CUDA(launch_kernel(ctc_prep_kernel, dim3((unsigned)(p.b1 - p.b0)), dim3(threads), sm, st,
+                          p.prep_after_stream != 0, p));
   return B200_OK;
 }
 
@@ -157,20 +157,28 @@ static int run_fused(LossParams p, int dtype, float* loss_sum, cudaStream_t st, 
   if (!rows_vec_ok(p.logits, p.V, p.stride_t, p.stride_b, es) ||
       !rows_vec_ok(p.grad, p.V, p.gstride_t, p.gstride_b, es) || !plan_stream(p, es, &sc))
     return B200_OK;
-  B200_CUDA(cudaMemsetAsync(p.ws.bad, 0, 64 * sizeof(int), st));
-  p.loss_sum = loss_sum;
+  p.loss_sum = loss_sum;  // (the prep kernel zeroes the workspace counters)
   // Running the sweeps UNDER the stream kernel (debug bit 4: prep fills lpg with NaN, the sweeps spin on
   // the words they need) was measured slower than running them after it (325 vs 278 us at C2): the
   // latency-bound sweep warps lose their issue slots to the 17 busy stream warps of the same SM.
   p.wait_rows = (p.debug & 4) ? 1 : 0;
-  int rc = launch_prep(p, st);
-  if (rc) return rc;
-  // stream, sweeps and patch are chained by programmatic dependent launch: the sweeps run UNDER
-  // the stream kernel (each waits for the rows of its own utterance), the patch is staged under
-  // the sweeps
+  // The stream kernel reads the int64 labels itself, so the 6 us label-prep kernel (int32 labels, duplicate
+  // codes, length ranking, workspace counters: inputs of the sweeps and of the patch) is launched AFTER it
+  // as a programmatic dependent and runs under it.  stream -> prep -> sweeps -> patch are all chained by
+  // programmatic dependent launch; every grid ends with griddepcontrol.wait so that completion is transitive.
+  p.prep_after_stream = p.wait_rows ? 0 : 1;
+  int rc = B200_OK;
+  if (!p.prep_after_stream) {
+    rc = launch_prep(p, st);
+    if (rc) return rc;
+  }
   rc = launch_stream(p, dtype, sc, st);
   if (rc) return rc;
   if (stream_only) { *done = true; return B200_OK; }
+  if (p.prep_after_stream) {
+    rc = launch_prep(p, st);
+    if (rc) return rc;
+  }
   rc = launch_sweep(p, st, true);
   if (rc) return rc;
   rc = launch_patch(p, dtype, st);

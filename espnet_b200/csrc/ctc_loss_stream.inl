@@ -91,7 +91,9 @@ __device__ __forceinline__ StreamRow stream_row(const LossParams& p, int64_t bas
   r.in_range = g < nrows;
   r.b = 0; r.t = 0; r.valid = false;
   if (r.in_range) {
-    r.b = p.ws.order[p.b0 + (int)(g / p.T)];  // longest utterances first: their sweeps start first
+    // (sweeps-under-stream experiment: longest utterances first, their sweeps start first; that order is a
+    // result of the prep kernel, which this kernel otherwise does not depend on)
+    r.b = p.wait_rows ? p.ws.order[p.b0 + (int)(g / p.T)] : p.b0 + (int)(g / p.T);
     r.t = (int)(g % p.T);
     r.valid = r.t < (int)p.ilen[r.b];
   }
@@ -141,10 +143,11 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
     mbar_fence_init();
   }
   __syncthreads();
-  // programmatic dependent launch: everything above overlapped the tail of the prep kernel; its
-  // results (labels, order) are needed from here on.  The lattice sweeps of this call may be
-  // staged from now on (they wait for this grid to finish).
-  pdl_wait();
+  // This kernel reads the caller's int64 labels itself (clamped exactly as the prep kernel clamps them), so
+  // it does not wait for the prep kernel: prep is launched AFTER it as a programmatic dependent and runs
+  // on the free thread slots of the SMs while the rows stream.  (Only the sweeps-under-stream experiment
+  // needs prep's results here.)
+  if (p.wait_rows) pdl_wait();
   pdl_launch_dependents();
 
   if (warp == kStreamWarps) {
@@ -207,14 +210,18 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
       const T* sT = reinterpret_cast<const T*>(sp);
       const int64_t row = (int64_t)b * p.T + t;
       const int L = (int)p.olen[b];
-      const int* lab = p.ws.labels + (int64_t)b * Kp;
+      const int64_t* tgt = p.targets + p.tgt_offsets[b];
+      auto label_at = [&](int k) -> int {
+        const int64_t v = tgt[k];
+        return (int)(v < 0 ? 0 : (v >= p.V ? p.V - 1 : v));
+      };
       const float wgt = p.grad_scale * (p.grad_weight ? p.grad_weight[b] : 1.0f);
       // columns this thread gathers (global loads issued before the row is waited for)
       int col[kStreamGather];
 #pragma unroll
       for (int g = 0; g < kStreamGather; ++g) {
         const int kk = gtid + GT * g;
-        col[g] = (kk >= 1 && kk <= L) ? lab[kk - 1] : p.blank;
+        col[g] = (kk >= 1 && kk <= L) ? label_at(kk - 1) : p.blank;
       }
 
       mbar_wait(&full[slot], (uint32_t)(round & 1));
@@ -229,7 +236,7 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
       // sweeps running under this kernel treat any non-NaN word of lpg as valid)
       float* park = p.ws.occ + row * Kp;
       for (int kk = gtid + GT * kStreamGather; kk <= L; kk += GT)
-        park[kk] = ElemTraits<T>::to_float(sT[lab[kk - 1]]) * B200_LOG2E;
+        park[kk] = ElemTraits<T>::to_float(sT[label_at(kk - 1)]) * B200_LOG2E;
       // Every thread of the group owns the vectors gtid + GT*u; the first nfull of them exist for
       // every thread (no bounds checks in the unrolled loops), at most one more for some.
       auto drive = [&](auto pass) {
@@ -357,8 +364,8 @@ static int launch_stream_t(const LossParams& p, const StreamCfg& c, cudaStream_t
   if (g > nrows) g = nrows;
   auto go = [&](auto kern) -> int {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem));
-    B200_CUDA(launch_kernel(kern, dim3((unsigned)g), dim3((kStreamWarps + 1) * 32), (size_t)c.smem, st, true, p,
-                            c.nslots, c.slot_bytes));
+    B200_CUDA(launch_kernel(kern, dim3((unsigned)g), dim3((kStreamWarps + 1) * 32), (size_t)c.smem, st,
+                            p.wait_rows != 0, p, c.nslots, c.slot_bytes));
     return B200_OK;
   };
   if (c.group == 1) return go(ctc_stream_kernel<T, 1>);

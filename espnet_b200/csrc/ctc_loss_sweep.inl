@@ -80,6 +80,8 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
   constexpr int kR = SweepRings<MAXT>::kR, kWR = SweepRings<MAXT>::kWR;
   static_assert(CHF == SweepRings<MAXT>::kCHF, "chunk size");
   pdl_launch_dependents();  // the occupancy kernel may be staged; it waits for this grid to finish
+  // order / labels come from the prep kernel, which runs under the stream kernel of the same call
+  if (!p.wait_rows) pdl_wait();
   const int b = p.ws.order[p.b0 + blockIdx.x];
   const int d = blockIdx.y;
   const int Tb = min((int)p.ilen[b], (int)p.T);
@@ -104,7 +106,6 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     return;
   }
   for (int k = i; k < nw * kR + kWR * nw; k += blockDim.x) s_bnd[k].tag = -1;
-  if (!p.wait_rows) pdl_wait();  // staged under the kernel that produces lpg: it is complete from here
   __syncthreads();
   if (warp >= nwa) return;
 
@@ -381,16 +382,12 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
   constexpr int kR = SweepRings<MAXT>::kR, kWR = SweepRings<MAXT>::kWR;
   static_assert(CHF == SweepRings<MAXT>::kCHF, "chunk size");
   pdl_launch_dependents();  // the occupancy kernel may be staged; it waits for this grid to finish
-  const int b = p.ws.order[p.b0 + blockIdx.x];
   const int d = blockIdx.y;
-  const int Tb = min((int)p.ilen[b], (int)p.T);
-  const int L = (int)p.olen[b];
   const int i = threadIdx.x;
   const int lane = i & 31, warp = i >> 5;
   const int nw = (blockDim.x >> 5) - 1;  // state warps launched; warp nw is the helper
   const int Kp = (int)p.ws.Kp;
   const int64_t Sp = p.ws.Sp;
-  const int nwa = L / 32 + 1;  // warps that own at least one state (threads 0..L)
   Tagged* s_bnd = reinterpret_cast<Tagged*>(sw_smem);  // [nw][kR] label state of lane 31 of warp w at frame f
   Tagged* s_wmx = s_bnd + (size_t)nw * kR;             // [kWR][nw] maximum over the states of warp w at the start of chunk c
   Tagged* s_ctl = s_wmx + (size_t)kWR * nw;            // [kCtlRing][2] {dstep, c}, {corr, c}
@@ -403,20 +400,28 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
   __shared__ int s_csum;
   __shared__ float s_neg;  // log(0), read as the label column of threads without a label
 
-  if (Tb <= 0) {
-    if (i == 0) {
-      if (d == 0) sweep_finish_nll(p, b, (L == 0) ? 0.0f : __int_as_float(0x7f800000));
-      else p.ws.logz_beta[b] = (L == 0) ? 0.0f : B200_NEG;
-    }
-    pdl_wait();
-    return;
-  }
+  // shared-memory set-up overlaps the tail of the previous kernels; everything after the wait may use the
+  // lpg rows of the stream kernel and the results of the prep kernel (utterance order, labels), which runs
+  // under the stream kernel
   for (int k = i; k < nw * kR + kWR * nw + 2 * kCtlRing; k += blockDim.x) s_bnd[k].tag = -1;
   if (i == 0) {
     s_neg = B200_NEG;
     for (int k = 0; k < kLpSlots; ++k) mbar_init(&s_bar[k], 1);
     mbar_fence_init();
     fence_proxy_async();
+  }
+  pdl_wait();
+  __syncthreads();
+  const int b = p.ws.order[p.b0 + blockIdx.x];
+  const int Tb = min((int)p.ilen[b], (int)p.T);
+  const int L = (int)p.olen[b];
+  const int nwa = L / 32 + 1;  // warps that own at least one state (threads 0..L)
+  if (Tb <= 0) {
+    if (i == 0) {
+      if (d == 0) sweep_finish_nll(p, b, (L == 0) ? 0.0f : __int_as_float(0x7f800000));
+      else p.ws.logz_beta[b] = (L == 0) ? 0.0f : B200_NEG;
+    }
+    return;
   }
   const int nfull = Tb / CHF;  // chunks 1 .. nfull-1 are full and take the fast path
   // logical frame f is physical frame f (alpha) or Tb-1-f (beta): rows of lpg and of the lattice
@@ -425,8 +430,6 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
   // the most skewed warp publishes its level of chunk m when warp 0 is around chunk m + nwa - 1; one more
   // pair of chunks lets the control record of chunk c be there when chunk c - 1 starts
   const int delay_p = (nwa + kP - 1) / kP * kP;
-  pdl_wait();  // staged under the kernel that produces lpg: it is complete from here
-  __syncthreads();
   if (warp >= nwa && warp != nw) return;
 
   if (warp == nw) {

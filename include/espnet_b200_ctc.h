@@ -134,7 +134,7 @@ int b200_ctc_loss_fwd_bwd(const void* logits, int dtype,
                           void* grad_logits, int64_t gstride_t, int64_t gstride_b,
                           void* workspace, size_t workspace_bytes, void* stream);
 
-/* Measurement aid: ONLY the first stage of b200_ctc_loss_fwd_bwd (label prep + the
+/* Measurement aid: ONLY the first stage of b200_ctc_loss_fwd_bwd (the
  * one pass over the logits: row statistics, label gather into the workspace and
  * grad_scale*grad_weight*softmax written to grad_logits).  bench.py times the
  * dominant HBM kernel with it; the result is not a gradient.  Returns
