@@ -102,6 +102,26 @@ class _CTCLossFunction(torch.autograd.Function):
         return grad, None, None, None, None, None, None
 
 
+def upload_valid_frames(x_host, x_dev, ilen):
+    """Host -> device copy of a (B,T,V) batch of logits that moves only the frames t < ilen[b] of
+    every utterance (one contiguous block per utterance).  The kernels never read padded frames --
+    as ``torch.nn.CTCLoss`` ignores them through ``input_lengths`` -- and write exact zeros to their
+    gradient rows, so the padding does not have to cross PCIe.  x_host should be pinned; the copies
+    are asynchronous on the current stream.  Returns the number of bytes copied."""
+    if x_host.shape != x_dev.shape or x_host.dtype != x_dev.dtype or not x_dev.is_cuda:
+        raise RuntimeError("upload_valid_frames: x_host and x_dev must be (B,T,V) tensors of one dtype, x_dev on CUDA")
+    if not (x_host.is_contiguous() and x_dev.is_contiguous()):
+        raise RuntimeError("upload_valid_frames: both buffers must be (B,T,V) contiguous")
+    B, T, V = x_host.shape
+    nbytes = 0
+    for b, n in enumerate(ilen.tolist() if torch.is_tensor(ilen) else list(ilen)):
+        n = max(0, min(int(n), T))
+        if n:
+            x_dev[b, :n].copy_(x_host[b, :n], non_blocking=True)
+            nbytes += n * V * x_host.element_size()
+    return nbytes
+
+
 def ctc_nll(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0):
     """Per-utterance negative log-likelihood (B,) fp32 from pre-softmax logits (T,B,V).
 

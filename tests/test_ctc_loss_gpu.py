@@ -220,3 +220,30 @@ def test_c5_long_form_reduced_batch():
     rn, rg = _ref64(x.float(), ilen, olen, ys)
     np.testing.assert_allclose(nll, rn, rtol=TOL_F32)
     assert _normrel(grad, rg) <= TOL_BF16
+
+
+def test_upload_valid_frames_gives_the_same_result_as_a_full_copy():
+    """The kernels never read frames past ilen: a device buffer that only received the valid frames
+    (padding left as NaN) gives bitwise the results of a full host->device copy."""
+    from espnet_b200 import ctc_loss as CL
+
+    c = _cases.make_loss_case(6, 90, 256, 20, seed=321, dtype=torch.bfloat16)
+    x, ilen, olen, ys = c["x"], c["ilen"], c["olen"], c["ys"]
+    B, T, V = x.shape
+    host = x.pin_memory()
+    dev = torch.full_like(x, float("nan"), device="cuda")
+    nbytes = CL.upload_valid_frames(host, dev, ilen)
+    assert nbytes == int(ilen.clamp(max=T).sum()) * V * 2
+    for b in range(B):
+        n = int(ilen[b])
+        assert torch.equal(dev[b, :n].cpu(), x[b, :n])
+        assert torch.isnan(dev[b, n:].float()).all()
+    L = ys.shape[1]
+    off = torch.arange(B) * L
+    a = CL.ctc_loss_fwd_bwd(dev.transpose(0, 1), ys.cuda().reshape(-1), off, ilen, olen, L, grad_scale=1.0 / B)
+    r = CL.ctc_loss_fwd_bwd(x.cuda().transpose(0, 1), ys.cuda().reshape(-1), off, ilen, olen, L, grad_scale=1.0 / B)
+    torch.cuda.synchronize()
+    assert torch.equal(a[0], r[0]) and torch.equal(a[1], r[1])
+    assert torch.equal(a[2].view(torch.int16), r[2].view(torch.int16))
+    with pytest.raises(RuntimeError):
+        CL.upload_valid_frames(host, dev.float(), ilen)
