@@ -249,6 +249,11 @@ __device__ __forceinline__ float ld_cg_f32(const float* p) {
   asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
   return r;
 }
+__device__ __forceinline__ int ld_acquire_s32(const int* p) {
+  int r;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
+  return r;
+}
 __device__ __forceinline__ float ld_relaxed_f32(const float* p) {
   float r;
   asm volatile("ld.relaxed.gpu.global.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");

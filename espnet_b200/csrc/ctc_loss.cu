@@ -19,6 +19,7 @@ __global__ void ctc_prep_kernel(LossParams p) {
   // the counters of the kernels that follow (task queues, finished-sweep count) start at zero; this grid
   // completes before any of them runs, so no separate memset node is needed in front of a call
   if (blockIdx.x == 0 && threadIdx.x >= 1 && threadIdx.x < 8) p.ws.bad[threadIdx.x] = 0;
+  if (threadIdx.x == 0) p.ws.done[b] = 0;
   for (int64_t i = threadIdx.x; i < L; i += blockDim.x) {
     int64_t v = y[i];
     if (v < 0 || v >= p.V || v == p.blank) {

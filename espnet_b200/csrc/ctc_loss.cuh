@@ -44,6 +44,7 @@ struct LossWs {
                     //             [1], [2] task counters of the rowstats / gradient kernels, [4] utterances
                     //             whose nll is final; zeroed at the start of every call
   int* order;       // [B]         utterances by decreasing ilen (rank -> b): long lattices start first
+  int* done;        // [B]         finished sweeps of utterance b (2 = its alpha and beta lattices are complete)
   int64_t Kp, Sp;
   size_t bytes;
 };
@@ -71,6 +72,7 @@ inline LossWs carve_loss_ws(void* base, int64_t T, int64_t B, int64_t V, int64_t
   w.nll_ws = (float*)take(sizeof(float) * B);
   w.bad = (int*)take(sizeof(int) * 64);
   w.order = (int*)take(sizeof(int) * B);
+  w.done = (int*)take(sizeof(int) * B);
   w.bytes = off;
   return w;
 }

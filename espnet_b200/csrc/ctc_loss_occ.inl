@@ -66,18 +66,32 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
 
   // ---- this warp's share: a contiguous range [r0, r1) of the valid rows, in (utterance, frame) order.
   // Lengths are inputs of the call, so this runs before the wait on the sweeps.
+  // Utterances are taken SHORTEST FIRST (logical index i -> utterance order[nb - 1 - i]): their sweeps finish
+  // first.  The ranges are handed out through a ticket counter, and a warp waits for the completion flags of
+  // the utterances of its range only: CTAs of this grid that become resident while long sweeps are still
+  // running (on the SMs that host no sweep CTA, and on those whose sweep CTA has finished; a CTA of this
+  // kernel and a sweep CTA do not fit on one SM together) work through the finished utterances meanwhile.
   const int nb = p.b1 - p.b0;
-  auto frames_of = [&](int i) { return i < nb ? max(min((int)p.ilen[p.b0 + i], T_), 0) : 0; };
+  auto phys = [&](int i) { return p.ws.order[p.b0 + nb - 1 - i]; };
+  auto frames_of = [&](int i) { return i < nb ? max(min((int)p.ilen[phys(i)], T_), 0) : 0; };
+  auto wait_done = [&](int ub) {  // lane 0 only
+    while (ld_acquire_s32(p.ws.done + ub) < 2) __nanosleep(256);
+  };
   int tot = 0;
   for (int base = 0; base < nb; base += 32) tot += frames_of(base + lane);
   tot = __reduce_add_sync(0xffffffffu, tot);
   const int total_warps = gridDim.x * nwarps;
   const int chunk = (tot + total_warps - 1) / total_warps;
-  const int r0 = min((blockIdx.x * nwarps + warp) * chunk, tot);
+  for (;;) {
+  int ticket = 0;
+  if (lane == 0) ticket = atomicAdd(p.ws.bad + 5, 1);
+  ticket = __shfl_sync(0xffffffffu, ticket, 0);
+  const int r0 = min(ticket * chunk, tot);
   const int n = min(r0 + chunk, tot) - r0;
-  if (n <= 0) return;
-  // producer cursor (lane 0 issues copies `stages` rows ahead) and consumer cursor, both warp-uniform
-  int pb = 0, pt = 0, pTb = 0, pL = 0;
+  if (n <= 0) break;
+  // producer cursor (lane 0 issues copies `stages` rows ahead) and consumer cursor, both warp-uniform;
+  // pi / bi: logical (shortest-first) indices of the utterances pb / b
+  int pi = 0, pb = 0, pt = 0, pTb = 0, pL = 0;
   {
     int run = 0;
     for (int base = 0; base < nb; base += 32) {
@@ -92,7 +106,8 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
       const unsigned hit = __ballot_sync(0xffffffffu, v > 0 && r0 >= excl && r0 < excl + v);
       if (hit) {
         const int src = __ffs(hit) - 1;
-        pb = p.b0 + base + src;
+        pi = base + src;
+        pb = phys(pi);
         pt = r0 - __shfl_sync(0xffffffffu, excl, src);
         pTb = __shfl_sync(0xffffffffu, v, src);
         break;
@@ -101,18 +116,21 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
     }
     pL = (int)p.olen[pb];
   }
-  int b = pb, t = pt, Tb = pTb, L = pL;  // consumer
+  int bi = pi, b = pb, t = pt, Tb = pTb, L = pL;  // consumer
   float wgt = 1.f;
   bool poison = false;
   // next utterance with frames (there is one whenever this is called: the range has rows left)
-  auto next_utt = [&](int& ub, int& uTb, int& uL) {
+  auto next_utt = [&](int& ui, int& ub, int& uTb, int& uL) {
     do {
-      ++ub;
+      ++ui;
+      ub = phys(ui);
       uTb = max(min((int)p.ilen[ub], T_), 0);
     } while (uTb == 0);
     uL = (int)p.olen[ub];
   };
-  pdl_wait();  // staged under the sweeps: their lattices (and the streamed gradient) are complete from here
+  // the producer runs ahead of the consumer: it is the one that waits for the lattices of an utterance
+  if (lane == 0) wait_done(pb);
+  __syncwarp();
 
   // utterance-level state of the consumer: weight, label columns and duplicate codes
   auto enter = [&]() {
@@ -143,7 +161,11 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
       bulk_g2s(st + 2 * Sp, p.ws.lpg + row * Kp, nL, &bars[s]);
     }
     ++issued;
-    if (++pt == pTb && issued < n) { next_utt(pb, pTb, pL); pt = 0; }
+    if (++pt == pTb && issued < n) {
+      next_utt(pi, pb, pTb, pL);
+      pt = 0;
+      if (lane == 0) wait_done(pb);
+    }
   };
   for (int i = 0; i < min(stages, n); ++i) issue(i);
   enter();
@@ -292,12 +314,15 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
       r += cnt;
       t += cnt;
       if (t == Tb && r < n) {
-        next_utt(b, Tb, L);
+        next_utt(bi, b, Tb, L);
         t = 0;
         enter();
       }
     }
   }
+  }  // next ticket
+  // this grid must not be seen as finished before the sweeps it ran under
+  pdl_wait();
 }
 
 struct OccPlan {

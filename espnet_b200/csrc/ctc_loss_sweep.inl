@@ -79,9 +79,11 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
   extern __shared__ __align__(16) unsigned char sw_smem[];
   constexpr int kR = SweepRings<MAXT>::kR, kWR = SweepRings<MAXT>::kWR;
   static_assert(CHF == SweepRings<MAXT>::kCHF, "chunk size");
-  pdl_launch_dependents();  // the occupancy kernel may be staged; it waits for this grid to finish
   // order / labels come from the prep kernel, which runs under the stream kernel of the same call
   if (!p.wait_rows) pdl_wait();
+  // the occupancy kernel may be staged from here on: it starts after EVERY sweep CTA has passed the wait above,
+  // i.e. with prep complete (its counters zeroed), and follows the per-utterance completion flags
+  pdl_launch_dependents();
   const int b = p.ws.order[p.b0 + blockIdx.x];
   const int d = blockIdx.y;
   const int Tb = min((int)p.ilen[b], (int)p.T);
@@ -324,6 +326,10 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     const float logz2 = z + (float)csum;
     if (d == 0) sweep_finish_nll(p, b, feasible ? -B200_LN2 * logz2 : __int_as_float(0x7f800000));
     else p.ws.logz_beta[b] = feasible ? logz2 : B200_NEG;
+    // this direction's lattice of utterance b is complete (every state warp stored its last frame before the
+    // barrier above): the occupancy kernel may read it once both directions have signalled
+    __threadfence();
+    atomicAdd(p.ws.done + b, 1);
   }
   // this grid must not be seen as finished before the stream kernel it ran under
   if (p.wait_rows) pdl_wait();
@@ -381,7 +387,6 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
   extern __shared__ __align__(16) unsigned char sw_smem[];
   constexpr int kR = SweepRings<MAXT>::kR, kWR = SweepRings<MAXT>::kWR;
   static_assert(CHF == SweepRings<MAXT>::kCHF, "chunk size");
-  pdl_launch_dependents();  // the occupancy kernel may be staged; it waits for this grid to finish
   const int d = blockIdx.y;
   const int i = threadIdx.x;
   const int lane = i & 31, warp = i >> 5;
@@ -411,6 +416,9 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
     fence_proxy_async();
   }
   pdl_wait();
+  // the occupancy kernel may be staged from here on: it starts after EVERY sweep CTA has passed the wait above,
+  // i.e. with prep complete (its counters zeroed), and follows the per-utterance completion flags
+  pdl_launch_dependents();
   __syncthreads();
   const int b = p.ws.order[p.b0 + blockIdx.x];
   const int Tb = min((int)p.ilen[b], (int)p.T);
@@ -701,6 +709,10 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
     const float logz2 = z + (float)s_csum;
     if (d == 0) sweep_finish_nll(p, b, feasible ? -B200_LN2 * logz2 : __int_as_float(0x7f800000));
     else p.ws.logz_beta[b] = feasible ? logz2 : B200_NEG;
+    // this direction's lattice of utterance b is complete (every state warp stored its last frame before the
+    // barrier above): the occupancy kernel may read it once both directions have signalled
+    __threadfence();
+    atomicAdd(p.ws.done + b, 1);
   }
 }
 
