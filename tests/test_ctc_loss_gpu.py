@@ -247,3 +247,28 @@ def test_upload_valid_frames_gives_the_same_result_as_a_full_copy():
     assert torch.equal(a[2].view(torch.int16), r[2].view(torch.int16))
     with pytest.raises(RuntimeError):
         CL.upload_valid_frames(host, dev.float(), ilen)
+
+
+def test_repeated_calls_are_bitwise_identical_at_c2_size():
+    """The kernels of a call are chained by programmatic dependent launch and per-utterance completion
+    flags (prep runs under the stream kernel, the patch kernel under the sweeps); a missed dependency would
+    show up as run-to-run differences.  25 back-to-back calls on one workspace, ragged C2-shaped batch."""
+    from espnet_b200 import ctc_loss as CL
+
+    c = _cases.make_loss_case(64, 500, 5000, 150, seed=4321, dtype=torch.bfloat16)
+    B, L = 64, c["ys"].shape[1]
+    xt = c["x"].cuda().transpose(0, 1)
+    plan = CL._Plan(xt, c["ys"].cuda().view(-1), torch.arange(B) * L, c["ilen"], c["olen"], L, 0)
+    ref = None
+    for it in range(25):
+        grad = torch.full((B, 500, 5000), float("nan"), dtype=torch.bfloat16, device="cuda").transpose(0, 1)
+        nll, ls, g = CL.ctc_loss_fwd_bwd(xt, None, None, None, None, L, grad_scale=1.0 / B, grad_out=grad, plan=plan)
+        if it % 3 == 0:
+            torch.cuda.synchronize()
+        cur = (nll.clone(), ls.clone(), g.contiguous().view(torch.int16).clone())
+        if ref is None:
+            ref = cur
+        else:
+            assert torch.equal(cur[0], ref[0]) and torch.equal(cur[1], ref[1]), f"nll differs at call {it}"
+            assert torch.equal(cur[2], ref[2]), f"gradient differs at call {it}"
+    assert not torch.isnan(ref[2].view(torch.bfloat16).float()).any()
