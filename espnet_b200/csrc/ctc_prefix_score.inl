@@ -89,20 +89,150 @@ __global__ void __launch_bounds__(kScoreThreads) prefix_score_full_kernel(ScoreP
         psi = B200_LZ;
       } else if (c == p.eos) {
         psi = p.w.REND[h];
-      } else if ((int64_t)c == p.last_ids[h]) {
-        // the hypothesis' own last label: phi is r_prev[:,b] only (rare: one token per hypothesis)
-        float a = 0.f;
-        for (int t = p.start; t < p.end; ++t)
-          a = fmaf(p.w.EB[((int64_t)u * p.T + t - 1) * NHP + j],
-                   ex2f(fmaf(xu[(int64_t)t * p.V], B200_LOG2E, -mxl)), a);
-        psi = finish_psi(a, p.w.MB[h] + mx, x0);
       } else {
+        // (the hypothesis' own last label is overwritten by prefix_score_last_kernel)
         psi = finish_psi(acc[j], p.w.MA[h] + mx, x0);
       }
       const float sp = p.s_prev ? p.s_prev[h] : 0.f;
       p.log_psi[(int64_t)h * p.V + c] = psi;
       p.scores[(int64_t)h * p.V + c] = psi - sp;
     }
+  }
+}
+
+// The same for vocabularies with V % 4 == 0: FOUR consecutive tokens per thread.  The one-token kernel above
+// is bound by the shared-memory pipe (NH/4 16-byte reads of E per token and frame: 7.5 M warp-wide LDS.128
+// per step at C3); here a thread reads x with one 16-byte load per frame and every E value feeds four
+// accumulators, so the kernel is back on the HBM roofline (x read once per step for the whole beam).
+constexpr int kScore4Threads = 128;
+constexpr int kScore4Batch = 8;  // frames (16-byte loads) in flight per thread and register set; two sets
+
+template <int NH>
+__global__ void __launch_bounds__(kScore4Threads) prefix_score_full4_kernel(ScoreParams p) {
+  __shared__ __align__(16) float sE[kScoreTB * NH];
+  const int u = blockIdx.y;
+  const int c0 = 4 * (blockIdx.x * kScore4Threads + threadIdx.x);
+  const bool live = c0 < p.V;  // V % 4 == 0: all four tokens or none
+  const int cc = live ? c0 : p.V - 4;
+  const int NHP = p.w.NHP;
+  const float* xu = p.x + (int64_t)u * p.T * p.V + cc;
+  const float4 mx4 = *reinterpret_cast<const float4*>(p.xmax + (int64_t)u * p.V + cc);
+  const float mx[4] = {mx4.x, mx4.y, mx4.z, mx4.w};
+  float mxl[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) mxl[q] = mx[q] * B200_LOG2E;
+  float acc[4][NH];
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int j = 0; j < NH; ++j) acc[q][j] = 0.f;
+
+  for (int tb = p.start; tb < p.end; tb += kScoreTB) {
+    const int nt = min(kScoreTB, p.end - tb);
+    __syncthreads();
+    for (int i = threadIdx.x; i < nt * NH; i += kScore4Threads) {
+      const int f = i / NH, j = i - f * NH;
+      sE[i] = j < NHP ? p.w.EA[((int64_t)u * p.T + (tb - 1 + f)) * NHP + j] : 0.f;
+    }
+    __syncthreads();
+    auto load = [&](int f0, uint4(&xv)[kScore4Batch]) {
+#pragma unroll
+      for (int k = 0; k < kScore4Batch; ++k) {
+        const int f = min(f0 + k, nt - 1);
+        xv[k] = ld_nc_v4(xu + (int64_t)(tb + f) * p.V);
+      }
+    };
+    auto consume = [&](int f0, const uint4(&xv)[kScore4Batch]) {
+#pragma unroll
+      for (int k = 0; k < kScore4Batch; ++k) {
+        const int f = f0 + k;
+        if (f < nt) {
+          float xh[4];
+          xh[0] = ex2f(fmaf(__uint_as_float(xv[k].x), B200_LOG2E, -mxl[0]));
+          xh[1] = ex2f(fmaf(__uint_as_float(xv[k].y), B200_LOG2E, -mxl[1]));
+          xh[2] = ex2f(fmaf(__uint_as_float(xv[k].z), B200_LOG2E, -mxl[2]));
+          xh[3] = ex2f(fmaf(__uint_as_float(xv[k].w), B200_LOG2E, -mxl[3]));
+          const float4* e4 = reinterpret_cast<const float4*>(sE + f * NH);
+#pragma unroll
+          for (int j4 = 0; j4 < NH / 4; ++j4) {
+            const float4 e = e4[j4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              acc[q][4 * j4 + 0] = fmaf(e.x, xh[q], acc[q][4 * j4 + 0]);
+              acc[q][4 * j4 + 1] = fmaf(e.y, xh[q], acc[q][4 * j4 + 1]);
+              acc[q][4 * j4 + 2] = fmaf(e.z, xh[q], acc[q][4 * j4 + 2]);
+              acc[q][4 * j4 + 3] = fmaf(e.w, xh[q], acc[q][4 * j4 + 3]);
+            }
+          }
+        }
+      }
+    };
+    uint4 xa[kScore4Batch], xb[kScore4Batch];
+    load(0, xa);
+    for (int f0 = 0; f0 < nt; f0 += 2 * kScore4Batch) {
+      if (f0 + kScore4Batch < nt) load(f0 + kScore4Batch, xb);
+      consume(f0, xa);
+      if (f0 + 2 * kScore4Batch < nt) load(f0 + 2 * kScore4Batch, xa);
+      consume(f0 + kScore4Batch, xb);
+    }
+  }
+  if (!live) return;
+  float x0[4] = {B200_LZ, B200_LZ, B200_LZ, B200_LZ};  // r[0,n] = x[0,c]
+  if (p.output_len == 0) {
+    const float4 v = *reinterpret_cast<const float4*>(p.x + (int64_t)u * p.T * p.V + c0);
+    x0[0] = v.x; x0[1] = v.y; x0[2] = v.z; x0[3] = v.w;
+  }
+#pragma unroll
+  for (int j = 0; j < NH; ++j) {
+    if (j < p.n_hyps) {
+      const int h = u * p.n_hyps + j;
+      const float sp = p.s_prev ? p.s_prev[h] : 0.f;
+      float psi[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int c = c0 + q;
+        if (c == p.blank) {
+          psi[q] = B200_LZ;
+        } else if (c == p.eos) {
+          psi[q] = p.w.REND[h];
+        } else {
+          // (the hypothesis' own last label is overwritten by prefix_score_last_kernel)
+          psi[q] = finish_psi(acc[q][j], p.w.MA[h] + mx[q], x0[q]);
+        }
+      }
+      *reinterpret_cast<float4*>(p.log_psi + (int64_t)h * p.V + c0) = make_float4(psi[0], psi[1], psi[2], psi[3]);
+      *reinterpret_cast<float4*>(p.scores + (int64_t)h * p.V + c0) =
+          make_float4(psi[0] - sp, psi[1] - sp, psi[2] - sp, psi[3] - sp);
+    }
+  }
+}
+
+// The one candidate per hypothesis that repeats its last label: phi is r_prev[:,b] only
+// (ctc_prefix_score.py:136-142).  Inside the full-vocabulary kernels this was a 500-iteration serial loop
+// in one thread of almost every CTA, which the whole CTA waited for; here one warp per hypothesis sums over the
+// frames in parallel and overwrites the entry (launched after the full-vocabulary kernel).
+__global__ void __launch_bounds__(128) prefix_score_last_kernel(ScoreParams p) {
+  const int lane = threadIdx.x & 31;
+  const int h = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (h >= p.n_bh) return;
+  const int64_t c64 = p.last_ids[h];
+  if (c64 < 0 || c64 >= p.V || c64 == p.blank || c64 == p.eos) return;
+  const int c = (int)c64;
+  const int u = h / p.n_hyps, j = h - u * p.n_hyps;
+  const int NHP = p.w.NHP;
+  const float* xu = p.x + (int64_t)u * p.T * p.V + c;
+  const float mx = p.xmax[(int64_t)u * p.V + c];
+  const float mxl = mx * B200_LOG2E;
+  float a = 0.f;
+  for (int t = p.start + lane; t < p.end; t += 32)
+    a = fmaf(p.w.EB[((int64_t)u * p.T + t - 1) * NHP + j], ex2f(fmaf(ld_nc_f32(xu + (int64_t)t * p.V), B200_LOG2E, -mxl)), a);
+  a = warp_sum(a);
+  if (lane == 0) {
+    const float x0 = (p.output_len == 0) ? xu[0] : B200_LZ;
+    const float psi = finish_psi(a, p.w.MB[h] + mx, x0);
+    const float sp = p.s_prev ? p.s_prev[h] : 0.f;
+    p.log_psi[(int64_t)h * p.V + c] = psi;
+    p.scores[(int64_t)h * p.V + c] = psi - sp;
   }
 }
 
@@ -185,27 +315,41 @@ __global__ void prefix_select_kernel(SelectParams p) {
     p.r_new[((int64_t)t * 2 + 0) * p.n_new + k] = pn;
     p.r_new[((int64_t)t * 2 + 1) * p.n_new + k] = pb;
   }
-  for (int t0 = p.start; t0 < p.end; t0 += kSelUnroll) {
-    float xc[kSelUnroll], xb[kSelUnroll], rn[kSelUnroll], rb[kSelUnroll];
+  // One lane per survivor and T sequential frames: the loads of the next batch of frames are issued
+  // before the current batch is consumed (two register sets).
+  struct Batch { float xc[kSelUnroll], xb[kSelUnroll], rn[kSelUnroll], rb[kSelUnroll]; };
+  auto load = [&](int t0, Batch& q) {
 #pragma unroll
     for (int i = 0; i < kSelUnroll; ++i) {
-      const int t = min(t0 + i, p.end - 1);
-      xc[i] = ld_nc_f32(xu + (int64_t)t * p.V + c);
-      xb[i] = ld_nc_f32(xu + (int64_t)t * p.V + p.blank);
-      rn[i] = p.r_prev[((int64_t)(t - 1) * 2 + 0) * p.n_bh + h];
-      rb[i] = p.r_prev[((int64_t)(t - 1) * 2 + 1) * p.n_bh + h];
+      const int t = max(min(t0 + i, p.end - 1), p.start);
+      q.xc[i] = ld_nc_f32(xu + (int64_t)t * p.V + c);
+      q.xb[i] = ld_nc_f32(xu + (int64_t)t * p.V + p.blank);
+      q.rn[i] = p.r_prev[((int64_t)(t - 1) * 2 + 0) * p.n_bh + h];
+      q.rb[i] = p.r_prev[((int64_t)(t - 1) * 2 + 1) * p.n_bh + h];
     }
+  };
+  auto consume = [&](int t0, const Batch& q) {
 #pragma unroll
     for (int i = 0; i < kSelUnroll; ++i) {
       const int t = t0 + i;
       if (t < p.end) {
-        const float phi = is_last ? rb[i] : lse2_nat(rn[i], rb[i]);
-        const float nn = lse2_nat(pn, phi) + xc[i];
-        const float nb = lse2_nat(pn, pb) + xb[i];
+        const float phi = is_last ? q.rb[i] : lse2_nat(q.rn[i], q.rb[i]);
+        const float nn = lse2_nat(pn, phi) + q.xc[i];
+        const float nb = lse2_nat(pn, pb) + q.xb[i];
         pn = nn; pb = nb;
         p.r_new[((int64_t)t * 2 + 0) * p.n_new + k] = pn;
         p.r_new[((int64_t)t * 2 + 1) * p.n_new + k] = pb;
       }
+    }
+  };
+  if (p.start < p.end) {
+    Batch qa, qb;
+    load(p.start, qa);
+    for (int t0 = p.start; t0 < p.end; t0 += 2 * kSelUnroll) {
+      load(t0 + kSelUnroll, qb);
+      consume(t0, qa);
+      load(t0 + 2 * kSelUnroll, qa);
+      consume(t0 + kSelUnroll, qb);
     }
   }
   for (int t = max(p.end, p.start); t < p.T; ++t) {
@@ -214,5 +358,79 @@ __global__ void prefix_select_kernel(SelectParams p) {
   }
   p.s_new[k] = p.log_psi[(int64_t)h * p.V + c];
 }
+
+// The same with ONE WARP per survivor: lane i loads the inputs of frame t0 + i of a batch of 32 frames (and
+// computes phi for it), the next batch is loaded before the current one is consumed, and the recursion itself
+// runs in every lane, taking the inputs of frame f from lane f by shuffle; lane f keeps the values of frame f
+// and stores them after the batch.  The per-thread kernel above waits one DRAM latency per 8 frames (its loads
+// are 20 KB apart); here 64 frames are in flight per survivor and the chain is ex2 -> lg2 only.
+__global__ void __launch_bounds__(128) prefix_select_warp_kernel(SelectParams p) {
+  const int lane = threadIdx.x & 31;
+  const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (k >= p.n_new) return;
+  const int h = (int)p.parent[k], c = (int)p.token[k];
+  const int u = h / p.n_hyps;
+  const bool is_last = ((int64_t)c == p.last_ids[h]);
+  const float* xu = p.x + (int64_t)u * p.T * p.V;
+  const int pre = min(p.start, p.T);
+  // frames before the window keep log(0), except r[0,n] = x[0,c] for the first label (:130-131)
+  for (int t = lane; t < pre; t += 32) {
+    p.r_new[((int64_t)t * 2 + 0) * p.n_new + k] = (t == 0 && p.output_len == 0) ? xu[c] : B200_LZ;
+    p.r_new[((int64_t)t * 2 + 1) * p.n_new + k] = B200_LZ;
+  }
+  float pn = (pre == 1 && p.output_len == 0) ? xu[c] : B200_LZ, pb = B200_LZ;
+  struct In { float xc, xb, rn, rb; };
+  auto load = [&](int t0) {
+    In q;
+    const int t = max(min(t0 + lane, p.end - 1), p.start);
+    q.xc = ld_nc_f32(xu + (int64_t)t * p.V + c);
+    q.xb = ld_nc_f32(xu + (int64_t)t * p.V + p.blank);
+    q.rn = p.r_prev[((int64_t)(t - 1) * 2 + 0) * p.n_bh + h];
+    q.rb = p.r_prev[((int64_t)(t - 1) * 2 + 1) * p.n_bh + h];
+    return q;
+  };
+  if (p.start < p.end) {
+    In cur = load(p.start);
+    for (int t0 = p.start; t0 < p.end; t0 += 32) {
+      const In nxt = load(t0 + 32);
+      const float phi_l = is_last ? cur.rb : lse2_nat(cur.rn, cur.rb);
+      float my_n = B200_LZ, my_b = B200_LZ;
+      const int nf = min(32, p.end - t0);
+      if (nf == 32) {
+#pragma unroll
+        for (int f = 0; f < 32; ++f) {
+          const float phi = __shfl_sync(0xffffffffu, phi_l, f);
+          const float xc = __shfl_sync(0xffffffffu, cur.xc, f);
+          const float xb = __shfl_sync(0xffffffffu, cur.xb, f);
+          const float nn = lse2_nat(pn, phi) + xc;
+          const float nb = lse2_nat(pn, pb) + xb;
+          pn = nn; pb = nb;
+          if (lane == f) { my_n = pn; my_b = pb; }
+        }
+      } else {
+        for (int f = 0; f < nf; ++f) {
+          const float phi = __shfl_sync(0xffffffffu, phi_l, f);
+          const float xc = __shfl_sync(0xffffffffu, cur.xc, f);
+          const float xb = __shfl_sync(0xffffffffu, cur.xb, f);
+          const float nn = lse2_nat(pn, phi) + xc;
+          const float nb = lse2_nat(pn, pb) + xb;
+          pn = nn; pb = nb;
+          if (lane == f) { my_n = pn; my_b = pb; }
+        }
+      }
+      if (lane < nf) {
+        p.r_new[((int64_t)(t0 + lane) * 2 + 0) * p.n_new + k] = my_n;
+        p.r_new[((int64_t)(t0 + lane) * 2 + 1) * p.n_new + k] = my_b;
+      }
+      cur = nxt;
+    }
+  }
+  for (int t = max(p.end, p.start) + lane; t < p.T; t += 32) {
+    p.r_new[((int64_t)t * 2 + 0) * p.n_new + k] = B200_LZ;
+    p.r_new[((int64_t)t * 2 + 1) * p.n_new + k] = B200_LZ;
+  }
+  if (lane == 0) p.s_new[k] = p.log_psi[(int64_t)h * p.V + c];
+}
+
 
 }  // namespace b200
