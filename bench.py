@@ -242,7 +242,20 @@ def run_b200(args, rank, world, local_rank):
     if world > 1:
         import datetime
 
-        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
+        # NCCL prints its version banner on stdout when the communicator comes up (NCCL_DEBUG=VERSION on some
+        # boxes): keep stdout for the ONE JSON line by pointing fd 1 at stderr until the first collective is done
+        sys.stdout.flush()
+        saved_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
+            warm = torch.zeros(1, device=dev)
+            dist.all_reduce(warm)
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_fd, 1)
+            os.close(saved_fd)
     lib = _lib.load()
     batch = make_batch(1236 + rank, args.full_length)
     x_host = batch["x"].pin_memory()                      # (B,T,V) bf16, what ctc_lo produces
