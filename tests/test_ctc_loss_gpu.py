@@ -272,3 +272,16 @@ def test_repeated_calls_are_bitwise_identical_at_c2_size():
             assert torch.equal(cur[0], ref[0]) and torch.equal(cur[1], ref[1]), f"nll differs at call {it}"
             assert torch.equal(cur[2], ref[2]), f"gradient differs at call {it}"
     assert not torch.isnan(ref[2].view(torch.bfloat16).float()).any()
+
+
+def test_many_utterances_more_ctas_than_sms():
+    """B = 400 utterances: the sweep grid (800 CTAs), the prep grid running under the stream kernel and the
+    ticketed patch kernel all need several waves on 148 SMs; completion flags and counters must still line up."""
+    c = _cases.make_loss_case(400, 48, 64, 10, seed=77)
+    x, ilen, olen, ys = c["x"], c["ilen"], c["olen"], c["ys"]
+    for _ in range(2):
+        nll, grad, ls = _run(x, ilen, olen, ys)
+        rn, rg = _ref64(x, ilen, olen, ys)
+        np.testing.assert_allclose(nll, rn, rtol=TOL_F32)
+        np.testing.assert_allclose(ls, rn.sum(), rtol=TOL_F32)
+        assert _normrel(grad, rg) <= TOL_F32
