@@ -95,8 +95,11 @@ extern "C" int b200_ctc_prefix_select(const float* x, int64_t B, int64_t T, int6
                                       const int64_t* parent, const int64_t* token, int64_t n_new,
                                       const float* work, float* r_new, float* s_new, void* stream) {
   (void)work;
-  B200_CHECK_ARG(x && r_prev && log_psi && last_ids && parent && token && r_new && s_new,
+  B200_CHECK_ARG(x && r_prev && log_psi && last_ids && parent && r_new && s_new,
                  B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(token != nullptr || (n_new > 0 && n_new % B == 0), B200_ERR_INVALID_ARGUMENT,
+                 "token is null (parent holds best_ids): n_new=%lld must be a multiple of B=%lld", (long long)n_new,
+                 (long long)B);
   B200_CHECK_ARG(B >= 1 && T >= 1 && V >= 2 && n_hyps >= 1 && n_bh == B * n_hyps, B200_ERR_INVALID_ARGUMENT,
                  "inconsistent sizes B=%lld n_hyps=%lld n_bh=%lld", (long long)B, (long long)n_hyps, (long long)n_bh);
   B200_CHECK_ARG(start >= 1 && end <= T, B200_ERR_INVALID_ARGUMENT, "bad frame window [%lld,%lld)",
@@ -108,6 +111,7 @@ extern "C" int b200_ctc_prefix_select(const float* x, int64_t B, int64_t T, int6
   p.r_prev = r_prev; p.log_psi = log_psi; p.last_ids = last_ids;
   p.output_len = (int)output_len; p.start = (int)start; p.end = (int)end;
   p.parent = parent; p.token = token; p.r_new = r_new; p.s_new = s_new;
+  p.beam = token ? 1 : (int)(n_new / B);
   // one warp per survivor (the one-lane-per-survivor kernel is kept for comparison: B200_DEBUG_VARIANT bit 2048)
   static const bool lane_kernel = getenv("B200_DEBUG_VARIANT") && (atoi(getenv("B200_DEBUG_VARIANT")) & 2048);
   if (lane_kernel) prefix_select_kernel<<<(unsigned)((n_new + 31) / 32), 32, 0, (cudaStream_t)stream>>>(p);

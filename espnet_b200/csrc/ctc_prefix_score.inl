@@ -314,17 +314,31 @@ struct SelectParams {
   const int64_t* last_ids;
   int output_len, start, end;
   const int64_t* parent;
-  const int64_t* token;
+  const int64_t* token;  // null: parent[] holds beam-pruning ids in (hypothesis * V + token) space, `beam` per utterance
+  int beam;
   float* r_new;  // (T,2,n_new)
   float* s_new;  // (n_new)
 };
 
 constexpr int kSelUnroll = 8;
 
+// parent hypothesis and appended token of survivor k (ctc_prefix_score.py:203-207 when only best_ids is given)
+__device__ __forceinline__ void select_pair(const SelectParams& p, int k, int& h, int& c) {
+  if (p.token) {
+    h = (int)p.parent[k];
+    c = (int)p.token[k];
+  } else {
+    const int64_t best = p.parent[k];
+    h = (int)(best / p.V) + (k / p.beam) * p.n_hyps;
+    c = (int)(best % p.V);
+  }
+}
+
 __global__ void prefix_select_kernel(SelectParams p) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= p.n_new) return;
-  const int h = (int)p.parent[k], c = (int)p.token[k];
+  int h, c;
+  select_pair(p, k, h, c);
   const int u = h / p.n_hyps;
   const bool is_last = ((int64_t)c == p.last_ids[h]);
   const float* xu = p.x + (int64_t)u * p.T * p.V;
@@ -389,7 +403,8 @@ __global__ void __launch_bounds__(128) prefix_select_warp_kernel(SelectParams p)
   const int lane = threadIdx.x & 31;
   const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (k >= p.n_new) return;
-  const int h = (int)p.parent[k], c = (int)p.token[k];
+  int h, c;
+  select_pair(p, k, h, c);
   const int u = h / p.n_hyps;
   const bool is_last = ((int64_t)c == p.last_ids[h]);
   const float* xu = p.x + (int64_t)u * p.T * p.V;

@@ -160,7 +160,8 @@ class CTCPrefixScoreB200(object):
         """r (T,2,n_new) and s (n_new,) of the hypotheses parent[k] extended by token[k]."""
         pending, log_psi, f_min, f_max, _ = state
         parent = parent.to(device=self.device, dtype=torch.int64).contiguous()
-        token = token.to(device=self.device, dtype=torch.int64).contiguous()
+        if token is not None:
+            token = token.to(device=self.device, dtype=torch.int64).contiguous()
         n_new = parent.numel()
         T, O = self.input_length, self.odim
         n_hyps = pending.n_bh // self.batch
@@ -170,7 +171,7 @@ class CTCPrefixScoreB200(object):
             rc = self._lib.b200_ctc_prefix_select(
                 self.x.data_ptr(), self.batch, T, O, n_hyps, self.blank, pending.r_prev.data_ptr(),
                 log_psi.data_ptr(), pending.last_ids.data_ptr(), pending.output_length, pending.start,
-                pending.end, pending.n_bh, parent.data_ptr(), token.data_ptr(), n_new, None,
+                pending.end, pending.n_bh, parent.data_ptr(), None if token is None else token.data_ptr(), n_new, None,
                 r_new.data_ptr(), s_new.data_ptr(), self._stream())
         _lib.check(rc, "b200_ctc_prefix_select")
         return r_new, s_new, f_min, f_max
@@ -182,11 +183,6 @@ class CTCPrefixScoreB200(object):
         :param best_ids: index numbers selected by beam pruning (B, W), in hyp * O + token space
         :return: (r_new (T,2,B*W), s_new (B*W,), f_min, f_max)
         """
-        pending = state[0]
-        n_hyps = pending.n_bh // self.batch
-        best_ids = best_ids.to(self.device)
-        parent = (torch.div(best_ids, self.odim, rounding_mode="floor")
-                  + (self.idx_b * n_hyps).view(-1, 1)).view(-1)
-        token = torch.fmod(best_ids, self.odim).view(-1)
-        return self.select(state, parent, token)
+        # parent = best_ids // O + utterance * n_hyps and token = best_ids % O are derived inside the kernel
+        return self.select(state, best_ids.reshape(self.batch, -1), None)
 

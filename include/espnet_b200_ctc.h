@@ -191,7 +191,11 @@ int b200_ctc_prefix_score(const float* x, const float* xmax, const int64_t* xlen
  * parent hypothesis parent[k] (index into the n_bh prefixes of the step that
  * produced `work`) and appended token token[k]:
  *   r_new[t,:,k] for t in [0,T)   and   s_new[k] = log_psi[parent[k], token[k]].
- * Uses the phi rows that b200_ctc_prefix_score left in `work`. */
+ * Uses the phi rows that b200_ctc_prefix_score left in `work`.
+ * token == NULL: parent[] holds the ids selected by beam pruning in
+ * (local hypothesis * V + token) space, n_new / B per utterance, as
+ * index_select_state receives them (ctc_prefix_score.py:203-207); the kernel
+ * derives parent and token itself. */
 int b200_ctc_prefix_select(const float* x, int64_t B, int64_t T, int64_t V,
                            int64_t n_hyps, int blank,
                            const float* r_prev, const float* log_psi,
