@@ -38,12 +38,14 @@ static void launch_full(const ScoreParams& p, cudaStream_t st) {
   // four tokens per thread when the rows of x, xmax, scores and log_psi can be read / written 16 bytes at a time
   const bool vec4 = p.V % 4 == 0 && NH <= 16 && ((uintptr_t)p.x | (uintptr_t)p.xmax | (uintptr_t)p.scores | (uintptr_t)p.log_psi) % 16 == 0;
   if (vec4) {
-    dim3 grid((unsigned)((p.V / 4 + kScore4Threads - 1) / kScore4Threads), (unsigned)p.B);
+    // row B of the grid: the repeated-last-label entries
+    dim3 grid((unsigned)((p.V / 4 + kScore4Threads - 1) / kScore4Threads), (unsigned)p.B + 1);
     prefix_score_full4_kernel<NH><<<grid, kScore4Threads, 0, st>>>(p);
     return;
   }
   dim3 grid((unsigned)((p.V + kScoreThreads - 1) / kScoreThreads), (unsigned)p.B);
   prefix_score_full_kernel<NH><<<grid, kScoreThreads, 0, st>>>(p);
+  prefix_score_last_kernel<<<(unsigned)((p.n_bh + 3) / 4), 128, 0, st>>>(p);
 }
 
 extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const int64_t* xlens, int64_t B, int64_t T,
@@ -76,8 +78,6 @@ extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const in
     else if (n_hyps <= 12) launch_full<12>(p, st);
     else if (n_hyps <= 16) launch_full<16>(p, st);
     else launch_full<32>(p, st);
-    B200_CUDA(cudaGetLastError());
-    prefix_score_last_kernel<<<(unsigned)((p.n_bh + 3) / 4), 128, 0, st>>>(p);
   } else {
     dim3 grid((unsigned)((V + 1023) / 1024), (unsigned)p.n_bh);
     prefix_fill_kernel<<<grid, 256, 0, st>>>(p);

@@ -100,6 +100,37 @@ __global__ void __launch_bounds__(kScoreThreads) prefix_score_full_kernel(ScoreP
   }
 }
 
+// The one candidate per hypothesis that repeats its last label: phi is r_prev[:,b] only
+// (ctc_prefix_score.py:136-142).  Inside the per-token loop of the full-vocabulary kernels this was a
+// 500-iteration serial loop in one thread of almost every CTA, which the whole CTA waited for; here one warp per
+// hypothesis sums over the frames in parallel and writes the entry.
+__device__ __forceinline__ void prefix_score_last_warp(const ScoreParams& p, int h, int lane) {
+  const int64_t c64 = p.last_ids[h];
+  if (c64 < 0 || c64 >= p.V || c64 == p.blank || c64 == p.eos) return;
+  const int c = (int)c64;
+  const int u = h / p.n_hyps, j = h - u * p.n_hyps;
+  const int NHP = p.w.NHP;
+  const float* xu = p.x + (int64_t)u * p.T * p.V + c;
+  const float mx = p.xmax[(int64_t)u * p.V + c];
+  const float mxl = mx * B200_LOG2E;
+  float a = 0.f;
+  for (int t = p.start + lane; t < p.end; t += 32)
+    a = fmaf(p.w.EB[((int64_t)u * p.T + t - 1) * NHP + j], ex2f(fmaf(ld_nc_f32(xu + (int64_t)t * p.V), B200_LOG2E, -mxl)), a);
+  a = warp_sum(a);
+  if (lane == 0) {
+    const float x0 = (p.output_len == 0) ? xu[0] : B200_LZ;
+    const float psi = finish_psi(a, p.w.MB[h] + mx, x0);
+    const float sp = p.s_prev ? p.s_prev[h] : 0.f;
+    p.log_psi[(int64_t)h * p.V + c] = psi;
+    p.scores[(int64_t)h * p.V + c] = psi - sp;
+  }
+}
+// (after the one-token kernel, which writes the generic value to that entry first)
+__global__ void __launch_bounds__(128) prefix_score_last_kernel(ScoreParams p) {
+  const int h = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (h < p.n_bh) prefix_score_last_warp(p, h, threadIdx.x & 31);
+}
+
 // The same for vocabularies with V % 4 == 0: FOUR consecutive tokens per thread.  The one-token kernel above
 // is bound by the shared-memory pipe (NH/4 16-byte reads of E per token and frame: 7.5 M warp-wide LDS.128
 // per step at C3); here every E value feeds four accumulators.  x is read ONCE per step for the whole beam,
@@ -124,6 +155,13 @@ template <int NH>
 __global__ void __launch_bounds__(kScore4Threads) prefix_score_full4_kernel(ScoreParams p) {
   __shared__ __align__(16) float sE[kScoreTB * NH];
   __shared__ __align__(16) uint4 sX[kScore4Ring * kScore4Batch * kScore4Threads];
+  if (blockIdx.y == (unsigned)p.B) {
+    // one more row of CTAs: the repeated-last-label entries, a warp per hypothesis (the token CTAs skip them)
+    const int nw = gridDim.x * (kScore4Threads / 32);
+    for (int h = blockIdx.x * (kScore4Threads / 32) + (threadIdx.x >> 5); h < p.n_bh; h += nw)
+      prefix_score_last_warp(p, h, threadIdx.x & 31);
+    return;
+  }
   const int u = blockIdx.y;
   const int c0 = 4 * (blockIdx.x * kScore4Threads + threadIdx.x);
   const bool live = c0 < p.V;  // V % 4 == 0: all four tokens or none
@@ -217,43 +255,24 @@ __global__ void __launch_bounds__(kScore4Threads) prefix_score_full4_kernel(Scor
         } else if (c == p.eos) {
           psi[q] = p.w.REND[h];
         } else {
-          // (the hypothesis' own last label is overwritten by prefix_score_last_kernel)
           psi[q] = finish_psi(acc[q][j], p.w.MA[h] + mx[q], x0[q]);
         }
       }
-      *reinterpret_cast<float4*>(p.log_psi + (int64_t)h * p.V + c0) = make_float4(psi[0], psi[1], psi[2], psi[3]);
-      *reinterpret_cast<float4*>(p.scores + (int64_t)h * p.V + c0) =
-          make_float4(psi[0] - sp, psi[1] - sp, psi[2] - sp, psi[3] - sp);
+      const int64_t last = p.last_ids[h];
+      if (last >= c0 && last < c0 + 4 && last != p.blank && last != p.eos) {
+        // the repeated-last-label entry belongs to the extra row of CTAs
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (c0 + q != (int)last) {
+            p.log_psi[(int64_t)h * p.V + c0 + q] = psi[q];
+            p.scores[(int64_t)h * p.V + c0 + q] = psi[q] - sp;
+          }
+      } else {
+        *reinterpret_cast<float4*>(p.log_psi + (int64_t)h * p.V + c0) = make_float4(psi[0], psi[1], psi[2], psi[3]);
+        *reinterpret_cast<float4*>(p.scores + (int64_t)h * p.V + c0) =
+            make_float4(psi[0] - sp, psi[1] - sp, psi[2] - sp, psi[3] - sp);
+      }
     }
-  }
-}
-
-// The one candidate per hypothesis that repeats its last label: phi is r_prev[:,b] only
-// (ctc_prefix_score.py:136-142).  Inside the full-vocabulary kernels this was a 500-iteration serial loop
-// in one thread of almost every CTA, which the whole CTA waited for; here one warp per hypothesis sums over the
-// frames in parallel and overwrites the entry (launched after the full-vocabulary kernel).
-__global__ void __launch_bounds__(128) prefix_score_last_kernel(ScoreParams p) {
-  const int lane = threadIdx.x & 31;
-  const int h = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (h >= p.n_bh) return;
-  const int64_t c64 = p.last_ids[h];
-  if (c64 < 0 || c64 >= p.V || c64 == p.blank || c64 == p.eos) return;
-  const int c = (int)c64;
-  const int u = h / p.n_hyps, j = h - u * p.n_hyps;
-  const int NHP = p.w.NHP;
-  const float* xu = p.x + (int64_t)u * p.T * p.V + c;
-  const float mx = p.xmax[(int64_t)u * p.V + c];
-  const float mxl = mx * B200_LOG2E;
-  float a = 0.f;
-  for (int t = p.start + lane; t < p.end; t += 32)
-    a = fmaf(p.w.EB[((int64_t)u * p.T + t - 1) * NHP + j], ex2f(fmaf(ld_nc_f32(xu + (int64_t)t * p.V), B200_LOG2E, -mxl)), a);
-  a = warp_sum(a);
-  if (lane == 0) {
-    const float x0 = (p.output_len == 0) ? xu[0] : B200_LZ;
-    const float psi = finish_psi(a, p.w.MB[h] + mx, x0);
-    const float sp = p.s_prev ? p.s_prev[h] : 0.f;
-    p.log_psi[(int64_t)h * p.V + c] = psi;
-    p.scores[(int64_t)h * p.V + c] = psi - sp;
   }
 }
 
