@@ -28,11 +28,13 @@ SIGNATURES = {
     "b200_ctc_loss_stream_pass": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp,
                                          _i64, _int, _vp, _f32, _vp, _i64, _i64, _vp, _sz, _vp]),
     "b200_ctc_prefix_init": (_int, [_vp, _vp, _i64, _i64, _i64, _int, _vp, _vp, _vp]),
-    "b200_ctc_prefix_work_floats": (_sz, [_i64, _i64]),
+    "b200_ctc_prefix_work_floats": (_sz, [_i64, _i64, _i64]),
     "b200_ctc_prefix_score": (_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _int, _int, _vp, _vp,
                                      _vp, _i64, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
     "b200_ctc_prefix_select": (_int, [_vp, _i64, _i64, _i64, _i64, _int, _vp, _vp, _vp, _i64,
                                       _i64, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
+    "b200_ctc_loss_status": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp]),
+    "b200_ctc_grad_rescale": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _i64, _f32, _vp, _vp]),
     "b200_ctc_greedy": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _vp]),
     "b200_ctc_viterbi_work_bytes": (_sz, [_i64, _i64]),
     "b200_ctc_viterbi": (_int, [_vp, _i64, _i64, _vp, _i64, _int, _vp, _vp, _sz, _vp]),

@@ -10,7 +10,9 @@ namespace b200 {
 __global__ void ctc_prep_kernel(LossParams p) {
   pdl_launch_dependents();  // the stream kernel may be staged (it waits for this grid before it reads labels)
   const int b = p.b0 + blockIdx.x;
-  const int64_t L = p.olen[b];
+  // olen beyond the Lmax the workspace was sized for is clamped (and flagged): nothing below may index past Kp
+  const int64_t Lraw = p.olen[b];
+  const int64_t L = Lraw < 0 ? 0 : (Lraw > p.Lmax ? p.Lmax : Lraw);
   const int64_t* y = p.targets + p.tgt_offsets[b];
   int* lab = p.ws.labels + (int64_t)b * p.ws.Kp;
   int* nxt = p.ws.dup_next + (int64_t)b * p.ws.Kp;
@@ -18,18 +20,23 @@ __global__ void ctc_prep_kernel(LossParams p) {
   extern __shared__ int s_lab[];
   // the counters of the kernels that follow (task queues, finished-sweep count) start at zero; this grid
   // completes before any of them runs, so no separate memset node is needed in front of a call
-  if (blockIdx.x == 0 && threadIdx.x >= 1 && threadIdx.x < 8) p.ws.bad[threadIdx.x] = 0;
-  if (threadIdx.x == 0) p.ws.done[b] = 0;
+  if (blockIdx.x == 0 && threadIdx.x < 8) p.ws.bad[threadIdx.x] = 0;
+  __shared__ int s_bad;
+  if (threadIdx.x == 0) { p.ws.done[b] = 0; s_bad = (Lraw != L) ? 1 : 0; }
+  __syncthreads();
   for (int64_t i = threadIdx.x; i < L; i += blockDim.x) {
     int64_t v = y[i];
     if (v < 0 || v >= p.V || v == p.blank) {
-      atomicExch(p.ws.bad, 1);
+      s_bad = 1;
       v = v < 0 ? 0 : (v >= p.V ? p.V - 1 : v);
     }
     s_lab[i] = (int)v;
     lab[i] = (int)v;
   }
   __syncthreads();
+  if (threadIdx.x == 0) {
+    p.ws.badutt[b] = s_bad;
+  }
   int* dc = p.ws.dupcode + (int64_t)b * p.ws.Kp;
   for (int64_t i = threadIdx.x; i < L; i += blockDim.x) {
     const int v = s_lab[i];
@@ -60,14 +67,6 @@ __global__ void ctc_prep_kernel(LossParams p) {
   }
   __syncthreads();
   if (threadIdx.x == 0) p.ws.order[p.b0 + s_rank] = b;
-  if (p.wait_rows) {
-    // fused call: the sweeps start before the stream kernel has produced lpg; NaN = "not yet"
-    const int Tb = min((int)p.ilen[b], (int)p.T);
-    uint4* dst = reinterpret_cast<uint4*>(p.ws.lpg + (int64_t)b * p.T * p.ws.Kp);  // Kp % 8 == 0: 16-byte rows
-    const int64_t n4 = (int64_t)Tb * p.ws.Kp / 4;
-    const uint4 nanv = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
-    for (int64_t k = threadIdx.x; k < n4; k += blockDim.x) dst[k] = nanv;
-  }
   // launched as a programmatic dependent of the stream kernel: this grid must not be seen as finished
   // before the kernel it ran under (the sweeps wait for THIS grid only)
   if (p.prep_after_stream) pdl_wait();

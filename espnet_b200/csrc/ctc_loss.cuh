@@ -40,9 +40,12 @@ struct LossWs {
   int* dupcode;     // [B][Kp]     both of the above packed (see kDupLater)
   float* logz_beta; // [B]         log2 p(y|x) from the beta sweep (consistency check)
   float* nll_ws;    // [B]         copy of nll (nats) kept for the backward pass
-  int* bad;         // [64 + B]    [0] set when a label is outside [0,V) or equals blank;
+  int* bad;         // [64]        [0] set when a label is outside [0,V) or equals blank, or olen > Lmax;
                     //             [1], [2] task counters of the rowstats / gradient kernels, [4] utterances
-                    //             whose nll is final; zeroed at the start of every call
+                    //             whose nll is final, [5] range tickets of the patch kernel; zeroed at the
+                    //             start of every call
+  int* badutt;      // [B]         1 if utterance b has an invalid label or olen[b] > Lmax: its nll is NaN and
+                    //             its gradient rows are NaN (a corrupt target batch must not train silently)
   int* order;       // [B]         utterances by decreasing ilen (rank -> b): long lattices start first
   int* done;        // [B]         finished sweeps of utterance b (2 = its alpha and beta lattices are complete)
   int64_t Kp, Sp;
@@ -71,6 +74,7 @@ inline LossWs carve_loss_ws(void* base, int64_t T, int64_t B, int64_t V, int64_t
   w.logz_beta = (float*)take(sizeof(float) * B);
   w.nll_ws = (float*)take(sizeof(float) * B);
   w.bad = (int*)take(sizeof(int) * 64);
+  w.badutt = (int*)take(sizeof(int) * B);
   w.order = (int*)take(sizeof(int) * B);
   w.done = (int*)take(sizeof(int) * B);
   w.bytes = off;
@@ -94,11 +98,15 @@ struct LossParams {
   float* nll;
   LossWs ws;
   int b0, b1;     // utterance range handled by this launch
-  int wait_rows;  // fused call: prep fills lpg with NaN, the sweeps run under the stream kernel and spin on
-                  // every lpg word they need until it is a number (the stream kernel never writes a NaN)
   float* loss_sum; // sum_b nll[b], written by the sweep CTA that finishes last (may be NULL)
-  int debug;      // developer experiments (B200_DEBUG_VARIANT), 0 in production
   int prep_after_stream;  // fused call: the prep kernel is a programmatic dependent of the stream kernel
 };
+
+// label count of utterance b as every kernel uses it: olen clamped to the Lmax the workspace was sized for
+// (the prep kernel flags the utterance when the clamp changes anything)
+__device__ __forceinline__ int utt_labels(const LossParams& p, int b) {
+  const int64_t L = p.olen[b];
+  return (int)(L < 0 ? 0 : (L > p.Lmax ? p.Lmax : L));
+}
 
 }  // namespace b200

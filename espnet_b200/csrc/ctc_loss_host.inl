@@ -114,7 +114,6 @@ static LossParams make_params(const void* logits, int64_t T, int64_t B, int64_t 
   p.nll = nll;
   p.ws = carve_loss_ws(workspace, T, B, V, Lmax);
   p.b0 = 0; p.b1 = (int)B;
-  { const char* e = getenv("B200_DEBUG_VARIANT"); p.debug = e ? atoi(e) : 0; }
   return p;
 }
 
@@ -153,32 +152,20 @@ static int run_fused(LossParams p, int dtype, float* loss_sum, cudaStream_t st, 
   *done = false;
   const int es = elem_size(dtype);
   StreamCfg sc;
-  if (p.debug & 1) return B200_OK;
   if (!rows_vec_ok(p.logits, p.V, p.stride_t, p.stride_b, es) ||
       !rows_vec_ok(p.grad, p.V, p.gstride_t, p.gstride_b, es) || !plan_stream(p, es, &sc))
     return B200_OK;
   p.loss_sum = loss_sum;  // (the prep kernel zeroes the workspace counters)
-  // Running the sweeps UNDER the stream kernel (debug bit 4: prep fills lpg with NaN, the sweeps spin on
-  // the words they need) was measured slower than running them after it (325 vs 278 us at C2): the
-  // latency-bound sweep warps lose their issue slots to the 17 busy stream warps of the same SM.
-  p.wait_rows = (p.debug & 4) ? 1 : 0;
   // The stream kernel reads the int64 labels itself, so the 6 us label-prep kernel (int32 labels, duplicate
   // codes, length ranking, workspace counters: inputs of the sweeps and of the patch) is launched AFTER it
   // as a programmatic dependent and runs under it.  stream -> prep -> sweeps -> patch are all chained by
   // programmatic dependent launch; every grid ends with griddepcontrol.wait so that completion is transitive.
-  p.prep_after_stream = p.wait_rows ? 0 : 1;
-  int rc = B200_OK;
-  if (!p.prep_after_stream) {
-    rc = launch_prep(p, st);
-    if (rc) return rc;
-  }
-  rc = launch_stream(p, dtype, sc, st);
+  p.prep_after_stream = 1;
+  int rc = launch_stream(p, dtype, sc, st);
   if (rc) return rc;
   if (stream_only) { *done = true; return B200_OK; }
-  if (p.prep_after_stream) {
-    rc = launch_prep(p, st);
-    if (rc) return rc;
-  }
+  rc = launch_prep(p, st);
+  if (rc) return rc;
   rc = launch_sweep(p, st, true);
   if (rc) return rc;
   rc = launch_patch(p, dtype, st);
@@ -290,5 +277,23 @@ extern "C" int b200_ctc_loss_stream_pass(const void* logits, int dtype, int64_t 
   rc = run_fused(p, dtype, nullptr, (cudaStream_t)stream, &done, true);
   if (rc) return rc;
   B200_CHECK_ARG(done, B200_ERR_UNSUPPORTED_SHAPE, "this shape runs on the three-pass path (no one-pass stream stage)");
+  return B200_OK;
+}
+
+extern "C" int b200_ctc_loss_status(const void* workspace, int64_t T, int64_t B, int64_t V, int64_t Lmax,
+                                    int32_t* n_invalid_host, void* stream) {
+  B200_CHECK_ARG(workspace && n_invalid_host, B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(T >= 1 && B >= 1 && V >= 1 && Lmax >= 0 && B < (1ll << 30), B200_ERR_INVALID_ARGUMENT, "bad sizes");
+  const LossWs ws = carve_loss_ws(const_cast<void*>(workspace), T, B, V, Lmax);
+  int* host = (int*)malloc(sizeof(int) * (size_t)B);
+  B200_CHECK_ARG(host != nullptr, B200_ERR_INVALID_ARGUMENT, "out of host memory");
+  cudaError_t e = cudaMemcpyAsync(host, ws.badutt, sizeof(int) * (size_t)B, cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize((cudaStream_t)stream);
+  int n = 0;
+  if (e == cudaSuccess)
+    for (int64_t b = 0; b < B; ++b) n += host[b] ? 1 : 0;
+  free(host);
+  if (e != cudaSuccess) return cuda_fail(e, "b200_ctc_loss_status");
+  *n_invalid_host = n;
   return B200_OK;
 }

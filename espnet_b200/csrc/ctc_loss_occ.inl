@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
   const int total_warps = gridDim.x * nwarps;
   // three ranges per warp of the grid (measured at C2: 190.4 / 186.7 / 185.7 / 187.0 / 188.3 us per step for
   // 1 / 2 / 3 / 4 / 6): early CTAs take more of them, but every range refills the warp's copy pipeline
-  const int split = ((p.debug >> 8) & 7) ? ((p.debug >> 8) & 7) : 3;
+  constexpr int split = 3;
   const int chunk = (tot + total_warps * split - 1) / (total_warps * split);
   for (;;) {
   int ticket = 0;
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
       }
       run += __shfl_sync(0xffffffffu, incl, 31);
     }
-    pL = (int)p.olen[pb];
+    pL = utt_labels(p, pb);
   }
   int bi = pi, b = pb, t = pt, Tb = pTb, L = pL;  // consumer
   float wgt = 1.f;
@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
       ub = phys(ui);
       uTb = max(min((int)p.ilen[ub], T_), 0);
     } while (uTb == 0);
-    uL = (int)p.olen[ub];
+    uL = utt_labels(p, ub);
   };
   // the producer runs ahead of the consumer: it is the one that waits for the lattices of an utterance
   if (lane == 0) wait_done(pb);
@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
   auto enter = [&]() {
     if (PATCH) {
       wgt = p.grad_scale * (p.grad_weight ? p.grad_weight[b] : 1.0f);
-      poison = isinf(p.ws.nll_ws[b]) || isnan(wgt);
+      poison = !isfinite(p.ws.nll_ws[b]) || isnan(wgt);
     }
     const int* lab = p.ws.labels + (int64_t)b * Kp;
     const int* dup = p.ws.dupcode + (int64_t)b * Kp;
@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
         // a 32-byte sector fill and write-back in DRAM.
         const T with = ElemTraits<T>::from_float(wgt * (pk - o * inv));
         const T without = ElemTraits<T>::from_float(wgt * pk);
-        if (raw_bits(with) != raw_bits(without) && !(p.debug & 16))
+        if (raw_bits(with) != raw_bits(without))
           grad[(int64_t)b * p.gstride_b + (int64_t)t * p.gstride_t + s_lab[k]] = with;
       } else {
         out[1 + k] = pk - o * inv;
@@ -304,7 +304,6 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
           T* dst = grad + (int64_t)b * p.gstride_b + (int64_t)(t + x) * p.gstride_t;
           for (int v = lane; v < (int)p.V; v += 32) dst[v] = nanv;
         }
-      } else if (p.debug & 32) {
       } else if constexpr (NJ > 0) {
         if (cnt == 2) process_regs(std::integral_constant<int, 2>{}, t, st);
         else process_regs(std::integral_constant<int, 1>{}, t, st);

@@ -88,7 +88,7 @@ __device__ __forceinline__ bool next_task(const LossParams& p, int* counter, int
   k->t0 = (q % nblk) * kFramesPerTask;
   k->t1 = min(k->t0 + kFramesPerTask, (int)p.T);
   k->Tb = (int)p.ilen[k->b];
-  k->L = (int)p.olen[k->b];
+  k->L = utt_labels(p, k->b);
   return true;
 }
 
@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(kGradMaxWarps * 32, 1) ctc_grad_kernel(LossPar
       col[i] = (k.t0 < k.Tb && kk >= 1 && kk <= L) ? s_lab[kk - 1] : p.blank;
     }
     const float wgt = p.grad_scale * (p.grad_weight ? p.grad_weight[k.b] : 1.0f);
-    const bool poison = isinf(p.ws.nll_ws[k.b]) || isnan(wgt);  // infeasible utterance: NaN rows (torch)
+    const bool poison = !isfinite(p.ws.nll_ws[k.b]) || isnan(wgt);  // infeasible utterance: NaN rows (torch)
     const bool neg = wgt < 0.f;
     const float lw = lg2f(fabsf(wgt));  // weight folded into the exponent; -inf for wgt == 0
 

@@ -91,9 +91,7 @@ __device__ __forceinline__ StreamRow stream_row(const LossParams& p, int64_t bas
   r.in_range = g < nrows;
   r.b = 0; r.t = 0; r.valid = false;
   if (r.in_range) {
-    // (sweeps-under-stream experiment: longest utterances first, their sweeps start first; that order is a
-    // result of the prep kernel, which this kernel otherwise does not depend on)
-    r.b = p.wait_rows ? p.ws.order[p.b0 + (int)(g / p.T)] : p.b0 + (int)(g / p.T);
+    r.b = p.b0 + (int)(g / p.T);
     r.t = (int)(g % p.T);
     r.valid = r.t < (int)p.ilen[r.b];
   }
@@ -145,9 +143,7 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
   __syncthreads();
   // This kernel reads the caller's int64 labels itself (clamped exactly as the prep kernel clamps them), so
   // it does not wait for the prep kernel: prep is launched AFTER it as a programmatic dependent and runs
-  // on the free thread slots of the SMs while the rows stream.  (Only the sweeps-under-stream experiment
-  // needs prep's results here.)
-  if (p.wait_rows) pdl_wait();
+  // on the free thread slots of the SMs while the rows stream.
   pdl_launch_dependents();
 
   if (warp == kStreamWarps) {
@@ -209,7 +205,7 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
       uint4* s4 = reinterpret_cast<uint4*>(sp);
       const T* sT = reinterpret_cast<const T*>(sp);
       const int64_t row = (int64_t)b * p.T + t;
-      const int L = (int)p.olen[b];
+      const int L = utt_labels(p, b);
       const int64_t* tgt = p.targets + p.tgt_offsets[b];
       auto label_at = [&](int k) -> int {
         const int64_t v = tgt[k];
@@ -365,7 +361,7 @@ static int launch_stream_t(const LossParams& p, const StreamCfg& c, cudaStream_t
   auto go = [&](auto kern) -> int {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem));
     B200_CUDA(launch_kernel(kern, dim3((unsigned)g), dim3((kStreamWarps + 1) * 32), (size_t)c.smem, st,
-                            p.wait_rows != 0, p, c.nslots, c.slot_bytes));
+                            false, p, c.nslots, c.slot_bytes));
     return B200_OK;
   };
   if (c.group == 1) return go(ctc_stream_kernel<T, 1>);

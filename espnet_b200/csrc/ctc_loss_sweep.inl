@@ -52,6 +52,7 @@ __device__ __forceinline__ float clamp_int_f(float x) {  // integer-valued, safe
 // Final value of utterance b; the CTA that delivers the last one also sums them (fixed order:
 // the sum is deterministic).
 __device__ __forceinline__ void sweep_finish_nll(const LossParams& p, int b, float nll) {
+  if (p.ws.badutt[b]) nll = __int_as_float(0x7fc00000);  // invalid labels / olen > Lmax: loud, not silent
   p.nll[b] = nll;
   p.ws.nll_ws[b] = nll;
   if (p.loss_sum == nullptr) return;
@@ -80,14 +81,14 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
   constexpr int kR = SweepRings<MAXT>::kR, kWR = SweepRings<MAXT>::kWR;
   static_assert(CHF == SweepRings<MAXT>::kCHF, "chunk size");
   // order / labels come from the prep kernel, which runs under the stream kernel of the same call
-  if (!p.wait_rows) pdl_wait();
+  pdl_wait();
   // the occupancy kernel may be staged from here on: it starts after EVERY sweep CTA has passed the wait above,
   // i.e. with prep complete (its counters zeroed), and follows the per-utterance completion flags
   pdl_launch_dependents();
   const int b = p.ws.order[p.b0 + blockIdx.x];
   const int d = blockIdx.y;
   const int Tb = min((int)p.ilen[b], (int)p.T);
-  const int L = (int)p.olen[b];
+  const int L = utt_labels(p, b);
   const int i = threadIdx.x;
   const int lane = i & 31, warp = i >> 5;
   const int nw = blockDim.x >> 5;
@@ -189,15 +190,7 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     }
     return corr;
   };
-  // lpg word that may not have been produced yet (fused call: NaN until the stream kernel writes it)
-  const bool spin = p.wait_rows != 0;
-  auto load_lp = [&](const float* q) -> float {
-    float v = ld_relaxed_f32(q);
-    if (spin) {
-      while (v != v) { __nanosleep(128); v = ld_relaxed_f32(q); }
-    }
-    return v;
-  };
+  auto load_lp = [&](const float* q) -> float { return ld_relaxed_f32(q); };
   // generic (slow) chunk: the first chunk and a trailing partial chunk; reads lpg directly
   auto slow_chunk = [&](int c, int n) {
     const int f0 = c * CHF;
@@ -220,12 +213,7 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     for (int f = 0; f < CHF; ++f) {
       if (f < n) {
         const int fr = f0 + f;
-        float lb_t = sb[f], ll_t = sl[f];
-        if (spin) {
-          const float* rowp = lp0 + (int64_t)fr * lstep;
-          if (lb_t != lb_t) lb_t = load_lp(rowp);
-          if (ll_t != ll_t) ll_t = load_lp(rowp + kcol);
-        }
+        const float lb_t = sb[f], ll_t = sl[f];
         if (fr == 0) {
           // frame 0: only the first blank and the first label are reachable
           if (i == 0) { ab = lb_t; al = ll_t; }
@@ -261,17 +249,6 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
   // the next wait on a load scoreboard (ptxas may give several load batches the same scoreboard)
   auto fast_chunk = [&](int c, float(&xb)[CHF], float(&xl)[CHF], float(&nb)[CHF], float(&nl)[CHF]) {
     const int f0 = c * CHF;
-    if (spin) {
-      // the prefetch may have run ahead of the stream kernel: reload until every word is a number
-      for (;;) {
-        bool missing = false;
-#pragma unroll
-        for (int f = 0; f < CHF; ++f) missing = missing || (xb[f] != xb[f]) || (xl[f] != xl[f]);
-        if (!__any_sync(0xffffffffu, missing)) break;
-        __nanosleep(128);
-        load_chunk(c, xb, xl);
-      }
-    }
     // first use of this chunk's registers (waits for their loads), then the prefetch
     float first = xb[0] + xl[0];
 #pragma unroll
@@ -331,8 +308,6 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
     __threadfence();
     atomicAdd(p.ws.done + b, 1);
   }
-  // this grid must not be seen as finished before the stream kernel it ran under
-  if (p.wait_rows) pdl_wait();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -422,7 +397,7 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
   __syncthreads();
   const int b = p.ws.order[p.b0 + blockIdx.x];
   const int Tb = min((int)p.ilen[b], (int)p.T);
-  const int L = (int)p.olen[b];
+  const int L = utt_labels(p, b);
   const int nwa = L / 32 + 1;  // warps that own at least one state (threads 0..L)
   if (Tb <= 0) {
     if (i == 0) {
@@ -758,8 +733,7 @@ namespace b200 {
 // pdl: staged under the stream kernel of the same call
 static int launch_sweep(const LossParams& p, cudaStream_t st, bool pdl = false) {
   const int threads = (int)align_up((size_t)(p.Lmax + 1), 32);
-  if (threads <= 256 && !p.wait_rows && !(p.debug & 64)) return launch_sweep_staged(p, threads, st, pdl);
-  if (threads <= 256) return launch_sweep_t<8, 256>(p, threads, st, pdl);
+  if (threads <= 256) return launch_sweep_staged(p, threads, st, pdl);
   return launch_sweep_t<4, 1024>(p, threads, st, pdl);
 }
 

@@ -140,9 +140,77 @@ __global__ void __launch_bounds__(1024) ctc_viterbi_kernel(const float* __restri
   }
 }
 
+// ------------------------------------------------------------------------------ gradient rescale
+// grad[t,b,:] *= gout[b] / expected for t < ilen[b]  (autograd backward of the one-pass call: the forward
+// already wrote expected * d nll_b / d logits; the upstream gradient is only known now).  Rows whose ratio is
+// exactly 1 -- the whole batch when the trainer's scale matches the hint -- are not touched: a CTA whose rows
+// all skip exits after reading B floats.
+template <typename T>
+__global__ void __launch_bounds__(256) ctc_grad_rescale_kernel(T* __restrict__ grad, int64_t Tn, int64_t B, int V,
+                                                               int64_t gstride_t, int64_t gstride_b,
+                                                               const float* __restrict__ gout, int gout_n, float expected,
+                                                               const int64_t* __restrict__ ilen) {
+  constexpr int PER = ElemTraits<T>::kPerVec;
+  const int nvec = V > 0 ? (int)((int64_t)V * sizeof(T) / 16) : 0;  // V < 0: rows are not 16-byte aligned
+  V = V > 0 ? V : -V;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const float inv = 1.0f / expected;
+  for (int64_t r = (int64_t)blockIdx.x * nwarp + warp; r < B * Tn; r += (int64_t)gridDim.x * nwarp) {
+    const int64_t b = r / Tn, t = r - b * Tn;
+    const float ratio = gout[gout_n == 1 ? 0 : b] * inv;
+    if (ratio == 1.0f) continue;
+    if (ilen && t >= ilen[b]) continue;  // zeros stay zeros
+    T* row = grad + b * gstride_b + t * gstride_t;
+    uint4* r4 = reinterpret_cast<uint4*>(row);
+    for (int j = lane; j < nvec; j += 32) {
+      float f[PER];
+      unpack16<T>(r4[j], f);
+#pragma unroll
+      for (int e = 0; e < PER; ++e) f[e] *= ratio;
+      r4[j] = pack16<T>(f);
+    }
+    for (int v = nvec * PER + lane; v < V; v += 32) row[v] = ElemTraits<T>::from_float(ElemTraits<T>::to_float(row[v]) * ratio);
+  }
+}
+
+template <typename T>
+static int launch_rescale(void* grad, int64_t Tn, int64_t B, int64_t V, int64_t gstride_t, int64_t gstride_b,
+                          const float* gout, int gout_n, float expected, const int64_t* ilen, cudaStream_t st) {
+  const int es = (int)sizeof(T);
+  const bool vec = (reinterpret_cast<uintptr_t>(grad) & 15) == 0 && (gstride_b * es) % 16 == 0 && (gstride_t * es) % 16 == 0;
+  int64_t g = (B * Tn + 7) / 8;
+  const int64_t cap = (int64_t)num_sms() * 8;
+  if (g > cap) g = cap;
+  // (unaligned rows: V is passed as 0 vectors by giving the scalar loop the whole row)
+  ctc_grad_rescale_kernel<T><<<(unsigned)g, 256, 0, st>>>((T*)grad, Tn, B, vec ? (int)V : -(int)V, gstride_t, gstride_b,
+                                                         gout, gout_n, expected, ilen);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_ctc_grad_rescale(void* grad, int dtype, int64_t T, int64_t B, int64_t V, int64_t gstride_t,
+                                     int64_t gstride_b, const float* gout, int64_t gout_n, float expected,
+                                     const int64_t* ilen, void* stream) {
+  B200_CHECK_ARG(grad && gout, B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(T >= 1 && B >= 1 && V >= 1 && V < (1ll << 30), B200_ERR_INVALID_ARGUMENT,
+                 "need T>=1, B>=1, 1<=V<2^30, got T=%lld B=%lld V=%lld", (long long)T, (long long)B, (long long)V);
+  B200_CHECK_ARG(gout_n == 1 || gout_n == B, B200_ERR_INVALID_ARGUMENT, "gout_n=%lld must be 1 or B=%lld",
+                 (long long)gout_n, (long long)B);
+  B200_CHECK_ARG(expected != 0.0f && expected == expected, B200_ERR_INVALID_ARGUMENT, "expected scale must be a non-zero number");
+  B200_CHECK_ARG(gstride_t >= 0 && gstride_b >= 0, B200_ERR_INVALID_ARGUMENT, "negative stride");
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (dtype) {
+    case B200_F32: return launch_rescale<float>(grad, T, B, V, gstride_t, gstride_b, gout, (int)gout_n, expected, ilen, st);
+    case B200_BF16: return launch_rescale<__nv_bfloat16>(grad, T, B, V, gstride_t, gstride_b, gout, (int)gout_n, expected, ilen, st);
+    case B200_F16: return launch_rescale<__half>(grad, T, B, V, gstride_t, gstride_b, gout, (int)gout_n, expected, ilen, st);
+  }
+  set_error("dtype must be B200_F32, B200_BF16 or B200_F16, got %d", dtype);
+  return B200_ERR_INVALID_ARGUMENT;
+}
 
 extern "C" int b200_ctc_greedy(const void* logits, int dtype, int64_t B, int64_t T, int64_t V, int64_t stride_b,
                                int64_t stride_t, int64_t* ids, void* stream) {

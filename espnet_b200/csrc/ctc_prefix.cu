@@ -65,6 +65,8 @@ struct PrefixWork {
   float* MA;    // [n_bh]
   float* MB;    // [n_bh]
   float* REND;  // [n_bh]  r_sum[xlen-1]
+  int* fix_count;  // [1]        pairs queued for the exact (log-space) kernel, zeroed by the phi kernel
+  int* fix_list;   // [n_bh * V] hypothesis * V + token
   int NHP;
 };
 
@@ -79,6 +81,8 @@ __host__ __device__ inline PrefixWork carve_prefix(float* work, int64_t B, int64
   w.MA = work + 2 * n;
   w.MB = w.MA + B * n_hyps;
   w.REND = w.MB + B * n_hyps;
+  w.fix_count = reinterpret_cast<int*>(w.REND + B * n_hyps);
+  w.fix_list = w.fix_count + 1;
   return w;
 }
 
@@ -89,6 +93,7 @@ __global__ void prefix_phi_kernel(const float* __restrict__ r_prev, const int64_
                                   int n_hyps, int n_bh, int start, int end, PrefixWork w) {
   const int h = blockIdx.x;
   const int u = h / n_hyps, j = h - u * n_hyps;
+  if (h == 0 && threadIdx.x == 0) *w.fix_count = 0;
   __shared__ float red[2][32];
   float ma = -3.0e38f, mb = -3.0e38f;
   for (int t = start - 1 + threadIdx.x; t < end - 1; t += blockDim.x) {

@@ -14,17 +14,18 @@ extern "C" int b200_ctc_prefix_init(float* x, const int64_t* xlens, int64_t B, i
   return B200_OK;
 }
 
-extern "C" size_t b200_ctc_prefix_work_floats(int64_t T, int64_t n_bh) {
-  if (T < 1 || n_bh < 1) return 0;
-  // 2 * B*T*pad4(n_hyps) + 3*n_bh, bounded by pad4(n_hyps)*B <= 4*n_bh
-  return (size_t)(2 * T * 4 * n_bh + 4 * n_bh);
+extern "C" size_t b200_ctc_prefix_work_floats(int64_t T, int64_t n_bh, int64_t V) {
+  if (T < 1 || n_bh < 1 || V < 1) return 0;
+  // 2 * B*T*pad4(n_hyps) + 3*n_bh, bounded by pad4(n_hyps)*B <= 4*n_bh; then the queue of the exact kernel
+  return (size_t)(2 * T * 4 * n_bh + 4 * n_bh + 4 + n_bh * V);
 }
 
 static int check_prefix(int64_t B, int64_t T, int64_t V, int64_t n_hyps, int blank, int64_t start, int64_t end) {
   B200_CHECK_ARG(B >= 1 && T >= 1 && V >= 2 && B < 65536, B200_ERR_INVALID_ARGUMENT,
                  "need 1<=B<65536, T>=1, V>=2, got B=%lld T=%lld V=%lld", (long long)B, (long long)T, (long long)V);
-  B200_CHECK_ARG(n_hyps >= 1 && n_hyps <= 32, B200_ERR_UNSUPPORTED_SHAPE,
-                 "n_hyps=%lld: 1..32 hypotheses per utterance are supported", (long long)n_hyps);
+  B200_CHECK_ARG(n_hyps >= 1 && n_hyps < (1 << 20), B200_ERR_INVALID_ARGUMENT, "n_hyps=%lld", (long long)n_hyps);
+  B200_CHECK_ARG(B * n_hyps * V < (1ll << 31), B200_ERR_UNSUPPORTED_SHAPE,
+                 "n_bh * V = %lld does not fit 31 bits", (long long)(B * n_hyps * V));
   B200_CHECK_ARG(blank >= 0 && blank < V, B200_ERR_INVALID_ARGUMENT, "blank=%d outside [0,%lld)", blank,
                  (long long)V);
   B200_CHECK_ARG(start >= 1 && end <= T, B200_ERR_INVALID_ARGUMENT,
@@ -72,12 +73,18 @@ extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const in
   p.w = carve_prefix(work, B, T, n_hyps);
   prefix_phi_kernel<<<p.n_bh, 128, 0, st>>>(r_prev, xlens, (int)T, (int)n_hyps, p.n_bh, p.start, p.end, p.w);
   B200_CUDA(cudaGetLastError());
+  p.hyp_off = 0;
   if (snum == 0) {
     if (n_hyps <= 4) launch_full<4>(p, st);
     else if (n_hyps <= 8) launch_full<8>(p, st);
     else if (n_hyps <= 12) launch_full<12>(p, st);
     else if (n_hyps <= 16) launch_full<16>(p, st);
-    else launch_full<32>(p, st);
+    else {
+      // wider beams (the LibriSpeech decode configs use beam_size 60): groups of 16 hypotheses, x is read once
+      // per group
+      for (; p.hyp_off < (int)n_hyps; p.hyp_off += 16) launch_full<16>(p, st);
+      p.hyp_off = 0;
+    }
   } else {
     dim3 grid((unsigned)((V + 1023) / 1024), (unsigned)p.n_bh);
     prefix_fill_kernel<<<grid, 256, 0, st>>>(p);
@@ -85,6 +92,9 @@ extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const in
     const int n = p.n_bh * p.snum;
     prefix_score_partial_kernel<<<(n + 127) / 128, 128, 0, st>>>(p);
   }
+  B200_CUDA(cudaGetLastError());
+  // pairs whose scaled sum underflowed: exact log-space redo (an empty queue costs one launch)
+  prefix_score_fix_kernel<<<2 * num_sms(), 256, 0, st>>>(p);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }
@@ -112,10 +122,7 @@ extern "C" int b200_ctc_prefix_select(const float* x, int64_t B, int64_t T, int6
   p.output_len = (int)output_len; p.start = (int)start; p.end = (int)end;
   p.parent = parent; p.token = token; p.r_new = r_new; p.s_new = s_new;
   p.beam = token ? 1 : (int)(n_new / B);
-  // one warp per survivor (the one-lane-per-survivor kernel is kept for comparison: B200_DEBUG_VARIANT bit 2048)
-  static const bool lane_kernel = getenv("B200_DEBUG_VARIANT") && (atoi(getenv("B200_DEBUG_VARIANT")) & 2048);
-  if (lane_kernel) prefix_select_kernel<<<(unsigned)((n_new + 31) / 32), 32, 0, (cudaStream_t)stream>>>(p);
-  else prefix_select_warp_kernel<<<(unsigned)((n_new + 3) / 4), 128, 0, (cudaStream_t)stream>>>(p);
+  prefix_select_warp_kernel<<<(unsigned)((n_new + 3) / 4), 128, 0, (cudaStream_t)stream>>>(p);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }

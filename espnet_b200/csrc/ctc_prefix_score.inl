@@ -18,7 +18,13 @@ struct ScoreParams {
   float* scores;   // (n_bh,V)
   float* log_psi;  // (n_bh,V)
   PrefixWork w;
+  int hyp_off;     // the full-vocabulary kernels handle hypotheses [hyp_off, hyp_off + NH) of every utterance
 };
+
+// The scaled linear sum loses every term below 2^-126 of the largest representable one (flush to zero).
+// With acc >= 2^-100 the at most T lost terms change log_psi by less than T * 2^-26 (< 1e-4 up to T = 6700);
+// below that the pair is queued for prefix_score_fix_kernel, which redoes it in log space.
+constexpr float kScoreAccFloor = 7.888609052210118e-31f;  // 2^-100
 
 __device__ __forceinline__ float finish_psi(float acc, float scale_log, float init_term) {
   // log( acc * exp(scale_log) + exp(init_term) ), with acc == 0 meaning log(0)
@@ -26,6 +32,13 @@ __device__ __forceinline__ float finish_psi(float acc, float scale_log, float in
   psi = fmaxf(psi, B200_LZ);
   if (init_term > B200_LZ) psi = lse2_nat(psi, init_term);
   return psi;
+}
+// queue (hypothesis h, token c) for the exact kernel
+__device__ __forceinline__ void score_flag(const ScoreParams& p, float acc, int h, int c) {
+  if (acc < kScoreAccFloor && p.start < p.end) {
+    const int k = atomicAdd(p.w.fix_count, 1);
+    p.w.fix_list[k] = h * p.V + c;
+  }
 }
 
 // All candidates: one thread per token, all hypotheses of the utterance at once.
@@ -49,7 +62,7 @@ __global__ void __launch_bounds__(kScoreThreads) prefix_score_full_kernel(ScoreP
     __syncthreads();
     // E rows for frames tb-1 .. tb+nt-2 (term t uses phi[t-1])
     for (int i = threadIdx.x; i < nt * NH; i += kScoreThreads) {
-      const int f = i / NH, j = i - f * NH;
+      const int f = i / NH, j = i - f * NH + p.hyp_off;
       sE[i] = j < NHP ? p.w.EA[((int64_t)u * p.T + (tb - 1 + f)) * NHP + j] : 0.f;
     }
     __syncthreads();
@@ -82,8 +95,8 @@ __global__ void __launch_bounds__(kScoreThreads) prefix_score_full_kernel(ScoreP
   const float x0 = (p.output_len == 0) ? p.x[(int64_t)u * p.T * p.V + c] : B200_LZ;  // r[0,n] = x[0,c]
 #pragma unroll
   for (int j = 0; j < NH; ++j) {
-    if (j < p.n_hyps) {
-      const int h = u * p.n_hyps + j;
+    if (j + p.hyp_off < p.n_hyps) {
+      const int h = u * p.n_hyps + j + p.hyp_off;
       float psi;
       if (c == p.blank) {
         psi = B200_LZ;
@@ -92,6 +105,7 @@ __global__ void __launch_bounds__(kScoreThreads) prefix_score_full_kernel(ScoreP
       } else {
         // (the hypothesis' own last label is overwritten by prefix_score_last_kernel)
         psi = finish_psi(acc[j], p.w.MA[h] + mx, x0);
+        if ((int64_t)c != p.last_ids[h]) score_flag(p, acc[j], h, c);
       }
       const float sp = p.s_prev ? p.s_prev[h] : 0.f;
       p.log_psi[(int64_t)h * p.V + c] = psi;
@@ -120,6 +134,7 @@ __device__ __forceinline__ void prefix_score_last_warp(const ScoreParams& p, int
   if (lane == 0) {
     const float x0 = (p.output_len == 0) ? xu[0] : B200_LZ;
     const float psi = finish_psi(a, p.w.MB[h] + mx, x0);
+    score_flag(p, a, h, c);
     const float sp = p.s_prev ? p.s_prev[h] : 0.f;
     p.log_psi[(int64_t)h * p.V + c] = psi;
     p.scores[(int64_t)h * p.V + c] = psi - sp;
@@ -157,6 +172,7 @@ __global__ void __launch_bounds__(kScore4Threads) prefix_score_full4_kernel(Scor
   __shared__ __align__(16) uint4 sX[kScore4Ring * kScore4Batch * kScore4Threads];
   if (blockIdx.y == (unsigned)p.B) {
     // one more row of CTAs: the repeated-last-label entries, a warp per hypothesis (the token CTAs skip them)
+    if (p.hyp_off != 0) return;  // (done by the launch of the first hypothesis group)
     const int nw = gridDim.x * (kScore4Threads / 32);
     for (int h = blockIdx.x * (kScore4Threads / 32) + (threadIdx.x >> 5); h < p.n_bh; h += nw)
       prefix_score_last_warp(p, h, threadIdx.x & 31);
@@ -200,7 +216,7 @@ __global__ void __launch_bounds__(kScore4Threads) prefix_score_full4_kernel(Scor
     const int nt = min(kScoreTB, p.end - tb);
     __syncthreads();
     for (int i = threadIdx.x; i < nt * NH; i += kScore4Threads) {
-      const int f = i / NH, j = i - f * NH;
+      const int f = i / NH, j = i - f * NH + p.hyp_off;
       sE[i] = j < NHP ? p.w.EA[((int64_t)u * p.T + (tb - 1 + f)) * NHP + j] : 0.f;
     }
     __syncthreads();
@@ -243,9 +259,10 @@ __global__ void __launch_bounds__(kScore4Threads) prefix_score_full4_kernel(Scor
   }
 #pragma unroll
   for (int j = 0; j < NH; ++j) {
-    if (j < p.n_hyps) {
-      const int h = u * p.n_hyps + j;
+    if (j + p.hyp_off < p.n_hyps) {
+      const int h = u * p.n_hyps + j + p.hyp_off;
       const float sp = p.s_prev ? p.s_prev[h] : 0.f;
+      const int64_t last = p.last_ids[h];
       float psi[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
@@ -256,9 +273,9 @@ __global__ void __launch_bounds__(kScore4Threads) prefix_score_full4_kernel(Scor
           psi[q] = p.w.REND[h];
         } else {
           psi[q] = finish_psi(acc[q][j], p.w.MA[h] + mx[q], x0[q]);
+          if ((int64_t)c != last) score_flag(p, acc[q][j], h, c);
         }
       }
-      const int64_t last = p.last_ids[h];
       if (last >= c0 && last < c0 + 4 && last != p.blank && last != p.eos) {
         // the repeated-last-label entry belongs to the extra row of CTAs
 #pragma unroll
@@ -319,9 +336,48 @@ __global__ void prefix_score_partial_kernel(ScoreParams p) {
   }
   const float x0 = (p.output_len == 0) ? xu[0] : B200_LZ;
   const float psi = finish_psi(a, (is_last ? p.w.MB[h] : p.w.MA[h]) + mx, x0);
+  score_flag(p, a, h, c);
   const float sp = p.s_prev ? p.s_prev[h] : 0.f;
   p.log_psi[(int64_t)h * p.V + c] = psi;
   p.scores[(int64_t)h * p.V + c] = psi - sp;
+}
+
+// Exact log-space redo of the queued (hypothesis, token) pairs (ctc_prefix_score.py:165-180 as written:
+// logsumexp over { r[start-1,n], phi[t-1] + x[t,c] }), one warp per pair.  The queue is empty for ordinary
+// posteriors; it fills when the joint spread of phi and x over the window exceeds what the scaled linear sum
+// holds (log-probs tens of nats apart between frames: saturated posteriors, windows that exclude the frames
+// that carry the mass).
+__global__ void __launch_bounds__(256) prefix_score_fix_kernel(ScoreParams p) {
+  const int lane = threadIdx.x & 31;
+  const int nw = gridDim.x * (blockDim.x >> 5);
+  const int n = min(*p.w.fix_count, p.n_bh * p.V);
+  for (int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); q < n; q += nw) {
+    const int code = p.w.fix_list[q];
+    const int h = code / p.V, c = code - h * p.V;
+    const int u = h / p.n_hyps;
+    const bool is_last = ((int64_t)c == p.last_ids[h]);
+    const float* xu = p.x + (int64_t)u * p.T * p.V + c;
+    float m = -3.0e38f, s = 0.f;  // running maximum and sum of exp(v - m), per lane
+    for (int t = p.start + lane; t < p.end; t += 32) {
+      const float rn = p.r_prev[((int64_t)(t - 1) * 2 + 0) * p.n_bh + h];
+      const float rb = p.r_prev[((int64_t)(t - 1) * 2 + 1) * p.n_bh + h];
+      const float v = (is_last ? rb : lse2_nat(rn, rb)) + ld_nc_f32(xu + (int64_t)t * p.V);
+      const float mn = fmaxf(m, v);
+      s = s * ex2f((m - mn) * B200_LOG2E) + ex2f((v - mn) * B200_LOG2E);
+      m = mn;
+    }
+    const float mw = warp_max(m);
+    s = warp_sum(s * ex2f((m - mw) * B200_LOG2E));
+    if (lane == 0) {
+      float psi = s > 0.f ? mw + B200_LN2 * lg2f(s) : B200_LZ;
+      psi = fmaxf(psi, B200_LZ);
+      const float x0 = (p.output_len == 0) ? xu[0] : B200_LZ;
+      if (x0 > B200_LZ) psi = lse2_nat(psi, x0);
+      const float sp = p.s_prev ? p.s_prev[h] : 0.f;
+      p.log_psi[(int64_t)h * p.V + c] = psi;
+      p.scores[(int64_t)h * p.V + c] = psi - sp;
+    }
+  }
 }
 
 // Forward variables of the survivors, ctc_prefix_score.py:123-131,157-162 in log space.
@@ -339,8 +395,6 @@ struct SelectParams {
   float* s_new;  // (n_new)
 };
 
-constexpr int kSelUnroll = 8;
-
 // parent hypothesis and appended token of survivor k (ctc_prefix_score.py:203-207 when only best_ids is given)
 __device__ __forceinline__ void select_pair(const SelectParams& p, int k, int& h, int& c) {
   if (p.token) {
@@ -353,67 +407,7 @@ __device__ __forceinline__ void select_pair(const SelectParams& p, int k, int& h
   }
 }
 
-__global__ void prefix_select_kernel(SelectParams p) {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= p.n_new) return;
-  int h, c;
-  select_pair(p, k, h, c);
-  const int u = h / p.n_hyps;
-  const bool is_last = ((int64_t)c == p.last_ids[h]);
-  const float* xu = p.x + (int64_t)u * p.T * p.V;
-  float pn = B200_LZ, pb = B200_LZ;
-  // frames before the window keep log(0), except r[0,n] = x[0,c] for the first label (:130-131)
-  for (int t = 0; t < min(p.start, p.T); ++t) {
-    pn = (t == 0 && p.output_len == 0) ? xu[c] : B200_LZ;
-    pb = B200_LZ;
-    p.r_new[((int64_t)t * 2 + 0) * p.n_new + k] = pn;
-    p.r_new[((int64_t)t * 2 + 1) * p.n_new + k] = pb;
-  }
-  // One lane per survivor and T sequential frames: the loads of the next batch of frames are issued
-  // before the current batch is consumed (two register sets).
-  struct Batch { float xc[kSelUnroll], xb[kSelUnroll], rn[kSelUnroll], rb[kSelUnroll]; };
-  auto load = [&](int t0, Batch& q) {
-#pragma unroll
-    for (int i = 0; i < kSelUnroll; ++i) {
-      const int t = max(min(t0 + i, p.end - 1), p.start);
-      q.xc[i] = ld_nc_f32(xu + (int64_t)t * p.V + c);
-      q.xb[i] = ld_nc_f32(xu + (int64_t)t * p.V + p.blank);
-      q.rn[i] = p.r_prev[((int64_t)(t - 1) * 2 + 0) * p.n_bh + h];
-      q.rb[i] = p.r_prev[((int64_t)(t - 1) * 2 + 1) * p.n_bh + h];
-    }
-  };
-  auto consume = [&](int t0, const Batch& q) {
-#pragma unroll
-    for (int i = 0; i < kSelUnroll; ++i) {
-      const int t = t0 + i;
-      if (t < p.end) {
-        const float phi = is_last ? q.rb[i] : lse2_nat(q.rn[i], q.rb[i]);
-        const float nn = lse2_nat(pn, phi) + q.xc[i];
-        const float nb = lse2_nat(pn, pb) + q.xb[i];
-        pn = nn; pb = nb;
-        p.r_new[((int64_t)t * 2 + 0) * p.n_new + k] = pn;
-        p.r_new[((int64_t)t * 2 + 1) * p.n_new + k] = pb;
-      }
-    }
-  };
-  if (p.start < p.end) {
-    Batch qa, qb;
-    load(p.start, qa);
-    for (int t0 = p.start; t0 < p.end; t0 += 2 * kSelUnroll) {
-      load(t0 + kSelUnroll, qb);
-      consume(t0, qa);
-      load(t0 + 2 * kSelUnroll, qa);
-      consume(t0 + kSelUnroll, qb);
-    }
-  }
-  for (int t = max(p.end, p.start); t < p.T; ++t) {
-    p.r_new[((int64_t)t * 2 + 0) * p.n_new + k] = B200_LZ;
-    p.r_new[((int64_t)t * 2 + 1) * p.n_new + k] = B200_LZ;
-  }
-  p.s_new[k] = p.log_psi[(int64_t)h * p.V + c];
-}
-
-// The same with ONE WARP per survivor: lane i loads the inputs of frame t0 + i of a batch of 32 frames (and
+// ONE WARP per survivor: lane i loads the inputs of frame t0 + i of a batch of 32 frames (and
 // computes phi for it), the next batch is loaded before the current one is consumed, and the recursion itself
 // runs in every lane, taking the inputs of frame f from lane f by shuffle; lane f keeps the values of frame f
 // and stores them after the batch.  The per-thread kernel above waits one DRAM latency per 8 frames (its loads

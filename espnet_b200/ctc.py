@@ -18,16 +18,57 @@ from .ctc_align import ctc_argmax, ctc_forced_align
 from .ctc_loss import ctc_nll
 
 
-def _b200_loss(th_pred, targets, tgt_offsets, th_ilen, th_olen, lmax, reduce):
-    """(T,B,V) pre-softmax logits -> CTCLoss(sum|none)(log_softmax(.)) / B."""
-    nll = ctc_nll(th_pred, targets, tgt_offsets, th_ilen, th_olen, lmax, blank=0)
+def _b200_loss(th_pred, targets, tgt_offsets, th_ilen, th_olen, lmax, reduce, hint=1.0, strict=False):
+    """(T,B,V) pre-softmax logits -> CTCLoss(sum|none)(log_softmax(.)) / B.
+
+    The one-pass kernels write the gradient during the forward call, scaled by the upstream gradient they
+    expect for nll_b: `hint` (what the trainer multiplies this loss by: ctc_weight / accum_grad x the AMP loss
+    scale; 1.0 for a bare ``loss.backward()``) divided by B.  Any other upstream gradient is honoured in
+    backward by one more pass over the gradient."""
+    B = th_pred.size(1)
+    nll = ctc_nll(th_pred, targets, tgt_offsets, th_ilen, th_olen, lmax, blank=0, grad_scale_hint=hint / B,
+                  strict=strict)
     loss = nll.sum() if reduce else nll
-    return loss / th_pred.size(1)
+    return loss / B
 
 
-def _concat_offsets(th_olen, device):
-    olen = torch.as_tensor(th_olen).to(device=device, dtype=torch.int64)
-    return torch.cumsum(olen, 0) - olen
+def _host_max(lens):
+    """max of a length vector without touching the device when the lengths are host values."""
+    if torch.is_tensor(lens):
+        return int(lens.max()) if lens.numel() else 0
+    return int(max(lens)) if len(lens) else 0
+
+
+def _viterbi_numpy(lpz, y, blank_id):
+    """Best CTC alignment on the host, the reference's recursion (pytorch_backend/ctc.py:153-216) with the inner
+    loop over states vectorised: float64 scores, candidates [s, s-1, s-2] with the first maximum kept, and the
+    reference's wrap-around reads (state -1 is the last state)."""
+    y = np.asarray(y, dtype=np.int64).reshape(-1)
+    ext = np.full(2 * len(y) + 1, blank_id, dtype=np.int64)
+    ext[1::2] = y
+    T, S = lpz.shape[0], len(ext)
+    sidx = np.arange(S)
+    two_only = (ext == blank_id) | (sidx < 2) | (ext == np.roll(ext, 2))
+    delta = np.full(S, -100000000000.0)
+    delta[0] = lpz[0, ext[0]]
+    if S > 1:
+        delta[1] = lpz[0, ext[1]]
+    back = np.full((T, S), -1, dtype=np.int16)
+    for t in range(1, T):
+        c1, c2 = np.roll(delta, 1), np.roll(delta, 2)
+        best, arg = delta.copy(), sidx.copy()
+        m = c1 > best
+        best[m], arg[m] = c1[m], sidx[m] - 1
+        m = (c2 > best) & ~two_only
+        best[m], arg[m] = c2[m], sidx[m] - 2
+        delta = best + lpz[t, ext].astype(np.float64)
+        back[t] = arg
+    st = S - 1 if delta[S - 1] >= delta[S - 2] else S - 2
+    states = np.empty(T, dtype=np.int64)
+    states[T - 1] = st
+    for t in range(T - 2, -1, -1):
+        states[t] = back[t + 1, states[t + 1]]
+    return [int(ext[k]) for k in states]
 
 
 class CTC(torch.nn.Module):
@@ -42,8 +83,13 @@ class CTC(torch.nn.Module):
     """
 
     def __init__(self, odim: int, encoder_output_sizse: int, dropout_rate: float = 0.0,
-                 ctc_type: str = "b200", reduce: bool = True):
+                 ctc_type: str = "b200", reduce: bool = True, grad_scale_hint: float = 1.0,
+                 strict_targets: bool = False):
         super().__init__()
+        # b200 only: the upstream gradient the trainer will send into this loss (see _b200_loss), and
+        # whether invalid targets raise (costs a host synchronisation per call) or give NaN
+        self.grad_scale_hint = grad_scale_hint
+        self.strict_targets = strict_targets
         eprojs = encoder_output_sizse
         self.dropout_rate = dropout_rate
         self.ctc_lo = torch.nn.Linear(eprojs, odim)
@@ -66,9 +112,12 @@ class CTC(torch.nn.Module):
     def loss_fn(self, th_pred, th_target, th_ilen, th_olen) -> torch.Tensor:
         """th_pred (T,B,V) logits, th_target 1-D concatenated labels (espnet2/asr/ctc.py:46)."""
         if self.ctc_type == "b200":
-            lmax = int(torch.as_tensor(th_olen).max()) if len(th_olen) else 0
-            off = _concat_offsets(th_olen, th_pred.device)
-            return _b200_loss(th_pred, th_target, off, th_ilen, th_olen, lmax, self.reduce)
+            # (lengths on the host, as espnet1 passes them, keep this free of device synchronisation)
+            lmax = _host_max(th_olen)
+            olen = torch.as_tensor(th_olen)
+            off = torch.cumsum(olen, 0) - olen
+            return _b200_loss(th_pred, th_target, off, th_ilen, olen, lmax, self.reduce, self.grad_scale_hint,
+                              self.strict_targets)
         elif self.ctc_type == "builtin":
             th_pred = th_pred.log_softmax(2)
             loss = self.ctc_loss(th_pred, th_target, th_ilen, th_olen)
@@ -106,7 +155,8 @@ class CTC(torch.nn.Module):
             B, lmax = ys_pad.size(0), ys_pad.size(1)
             ys_flat = ys_pad.contiguous().view(-1)
             off = torch.arange(B, device=ys_pad.device, dtype=torch.int64) * lmax
-            loss = _b200_loss(ys_hat, ys_flat, off, hlens, ys_lens, lmax, self.reduce)
+            loss = _b200_loss(ys_hat, ys_flat, off, hlens, ys_lens, lmax, self.reduce, self.grad_scale_hint,
+                              self.strict_targets)
         else:
             # (B, L) -> (BxL,)
             ys_true = torch.cat([ys_pad[i, :l] for i, l in enumerate(ys_lens)])
@@ -134,8 +184,11 @@ class CTCEspnet1(torch.nn.Module):
     :param bool reduce: reduce the CTC loss into a scalar
     """
 
-    def __init__(self, odim, eprojs, dropout_rate, ctc_type="b200", reduce=True):
+    def __init__(self, odim, eprojs, dropout_rate, ctc_type="b200", reduce=True, grad_scale_hint=1.0,
+                 strict_targets=False):
         super().__init__()
+        self.grad_scale_hint = grad_scale_hint  # b200 only, see _b200_loss
+        self.strict_targets = strict_targets
         self.dropout_rate = dropout_rate
         self.loss = None
         self.ctc_lo = torch.nn.Linear(eprojs, odim)
@@ -157,9 +210,11 @@ class CTCEspnet1(torch.nn.Module):
 
     def loss_fn(self, th_pred, th_target, th_ilen, th_olen):
         if self.ctc_type == "b200":
-            lmax = int(torch.as_tensor(th_olen).max()) if len(th_olen) else 0
-            off = _concat_offsets(th_olen, th_pred.device)
-            return _b200_loss(th_pred, th_target, off, th_ilen, th_olen, lmax, self.reduce)
+            lmax = _host_max(th_olen)
+            olen = torch.as_tensor(th_olen)
+            off = torch.cumsum(olen, 0) - olen
+            return _b200_loss(th_pred, th_target, off, th_ilen, olen, lmax, self.reduce, self.grad_scale_hint,
+                              self.strict_targets)
         elif self.ctc_type == "builtin":
             th_pred = th_pred.log_softmax(2)
             with torch.backends.cudnn.flags(deterministic=True):
@@ -210,8 +265,8 @@ class CTCEspnet1(torch.nn.Module):
         in ``b200_ctc_viterbi`` instead of a numpy double loop)."""
         lpz = self.log_softmax(h)
         lpz = lpz.squeeze(0)
-        if self.ctc_type != "b200":
-            raise NotImplementedError('forced_align is provided for ctc_type="b200" only')
+        if self.ctc_type != "b200" or not lpz.is_cuda:
+            return _viterbi_numpy(lpz.detach().cpu().numpy(), torch.as_tensor(y).cpu().numpy(), blank_id)
         return ctc_forced_align(lpz, y, blank_id)
 
 

@@ -6,6 +6,15 @@ fused into the kernels, so the functions here take PRE-softmax logits.
 
 All device work goes through the C ABI of ``libespnet_b200_ctc.so``
 (``include/espnet_b200_ctc.h``); torch only owns the memory and the stream.
+
+How autograd reaches the ONE-PASS kernels.  ``b200_ctc_loss_fwd_bwd`` reads the logits once and
+writes the gradient in the same call, but needs the upstream gradient d loss / d nll_b at forward
+time.  ``ctc_nll`` therefore runs it in ``forward`` with an EXPECTED upstream gradient
+(``grad_scale_hint``: what the caller will multiply nll_b by, 1/B in ``CTC.loss_fn``), keeps the
+finished gradient, and ``backward`` hands it out after ``b200_ctc_grad_rescale`` -- a kernel that
+compares the real upstream gradient with the expectation ON THE DEVICE (no host synchronisation)
+and touches only the rows whose ratio is not exactly 1.  When the trainer's scale equals the hint,
+``loss.backward()`` costs one launch of a kernel that reads B floats.
 """
 import torch
 
@@ -38,17 +47,38 @@ def _empty_like_strided(x):
     return torch.empty((T, B, V), dtype=x.dtype, device=x.device)
 
 
+def pack_labels(targets, tgt_offsets, ilen, olen, device):
+    """ONE host->device copy for the label side of a call: [targets | tgt_offsets | ilen | olen] as int64
+    in one pinned staging buffer (a step otherwise issues four small pageable copies, each a host
+    synchronisation).  Inputs that already live on `device` are used as they are.
+    Returns (targets, tgt_offsets, ilen, olen) as int64 device tensors."""
+    parts = [targets, tgt_offsets, ilen, olen]
+    parts = [p if torch.is_tensor(p) else torch.as_tensor(p) for p in parts]
+    host = [k for k, p in enumerate(parts) if not p.is_cuda]
+    out = list(parts)
+    if host:
+        sizes = [parts[k].numel() for k in host]
+        stage = torch.empty(sum(sizes), dtype=torch.int64, pin_memory=torch.device(device).type == "cuda")
+        o = 0
+        for k, n in zip(host, sizes):
+            stage[o:o + n].copy_(parts[k].reshape(-1))
+            o += n
+        dev = stage.to(device, non_blocking=True)
+        o = 0
+        for k, n in zip(host, sizes):
+            out[k] = dev[o:o + n]
+            o += n
+    return tuple(_as_i64(p, device) for p in out)
+
+
 class _Plan(object):
-    """Device-side arguments shared by forward and backward of one call."""
+    """Device-side arguments shared by the kernels of one call."""
 
     def __init__(self, logits, targets, tgt_offsets, ilen, olen, lmax, blank):
         dev = logits.device
         self.logits = logits
         self.T, self.B, self.V = logits.shape
-        self.targets = _as_i64(targets, dev)
-        self.tgt_offsets = _as_i64(tgt_offsets, dev)
-        self.ilen = _as_i64(ilen, dev)
-        self.olen = _as_i64(olen, dev)
+        self.targets, self.tgt_offsets, self.ilen, self.olen = pack_labels(targets, tgt_offsets, ilen, olen, dev)
         if self.ilen.numel() != self.B or self.olen.numel() != self.B or self.tgt_offsets.numel() != self.B:
             raise RuntimeError("ilen, olen and tgt_offsets must have one entry per utterance")
         self.lmax = int(lmax)
@@ -67,39 +97,77 @@ class _Plan(object):
                 self.targets.data_ptr(), self.tgt_offsets.data_ptr(), self.ilen.data_ptr(),
                 self.olen.data_ptr(), self.lmax, self.blank)
 
+    def invalid_utterances(self):
+        """Number of utterances of the last call on this plan whose targets were invalid (a label outside
+        [0,V) or equal to blank, or olen > lmax).  Synchronises the stream."""
+        import ctypes
+
+        n = ctypes.c_int32(0)
+        with torch.cuda.device(self.logits.device):
+            rc = _lib.load().b200_ctc_loss_status(self.ws_ptr, self.T, self.B, self.V, self.lmax, ctypes.byref(n),
+                                                  _stream(self.logits.device))
+        _lib.check(rc, "b200_ctc_loss_status")
+        return int(n.value)
+
 
 def _stream(device):
     return torch.cuda.current_stream(device).cuda_stream
 
 
+def _check_strict(plan):
+    n = plan.invalid_utterances()
+    if n:
+        raise ValueError(f"{n} utterance(s) with invalid CTC targets: labels must lie in [0, {plan.V}) and differ "
+                         f"from blank={plan.blank}, and olen must not exceed lmax={plan.lmax}")
+
+
 class _CTCLossFunction(torch.autograd.Function):
-    """nll (B,) fp32 = -log p(y_b | x_b); backward gives d/d logits."""
+    """nll (B,) fp32 = -log p(y_b | x_b); backward gives d/d logits.
+
+    With a gradient expected for the logits, forward runs the one-pass fused call with
+    grad_scale = `hint` and keeps the finished gradient; backward rescales it on the device where
+    the upstream gradient differs from the hint.  Without one (evaluation), forward only runs
+    the row statistics and the lattice sweeps."""
 
     @staticmethod
-    def forward(ctx, logits, targets, tgt_offsets, ilen, olen, lmax, blank):
+    def forward(ctx, logits, targets, tgt_offsets, ilen, olen, lmax, blank, hint, strict):
         logits = _prep_logits(logits.detach())
         plan = _Plan(logits, targets, tgt_offsets, ilen, olen, lmax, blank)
-        nll = torch.empty(plan.B, dtype=torch.float32, device=logits.device)
-        with torch.cuda.device(logits.device):
-            rc = _lib.load().b200_ctc_loss_forward(
-                *plan.common_args(), nll.data_ptr(), None, plan.ws_ptr, plan.ws_bytes,
-                _stream(logits.device))
-        _lib.check(rc, "b200_ctc_loss_forward")
-        ctx.plan = plan
+        dev = logits.device
+        nll = torch.empty(plan.B, dtype=torch.float32, device=dev)
+        ctx.hint = float(hint)
+        if ctx.needs_input_grad[0]:
+            grad = _empty_like_strided(logits)
+            with torch.cuda.device(dev):
+                rc = _lib.load().b200_ctc_loss_fwd_bwd(
+                    *plan.common_args(), None, ctx.hint, nll.data_ptr(), None, grad.data_ptr(),
+                    grad.stride(0), grad.stride(1), plan.ws_ptr, plan.ws_bytes, _stream(dev))
+            _lib.check(rc, "b200_ctc_loss_fwd_bwd")
+            ctx.save_for_backward(grad, plan.ilen)
+        else:
+            with torch.cuda.device(dev):
+                rc = _lib.load().b200_ctc_loss_forward(
+                    *plan.common_args(), nll.data_ptr(), None, plan.ws_ptr, plan.ws_bytes, _stream(dev))
+            _lib.check(rc, "b200_ctc_loss_forward")
+        if strict:
+            _check_strict(plan)
+        # the workspace goes back to the allocator here: reuse is ordered on this stream
         return nll
 
     @staticmethod
     def backward(ctx, grad_nll):
-        plan = ctx.plan
-        x = plan.logits
-        gw = grad_nll.to(dtype=torch.float32).contiguous()
-        grad = _empty_like_strided(x)
-        with torch.cuda.device(x.device):
-            rc = _lib.load().b200_ctc_loss_backward(
-                *plan.common_args(), gw.data_ptr(), 1.0, grad.data_ptr(), grad.stride(0),
-                grad.stride(1), plan.ws_ptr, plan.ws_bytes, _stream(x.device))
-        _lib.check(rc, "b200_ctc_loss_backward")
-        return grad, None, None, None, None, None, None
+        grad, ilen = ctx.saved_tensors
+        T, B, V = grad.shape
+        gw = grad_nll.to(dtype=torch.float32).reshape(-1)
+        if gw.numel() > 1 and gw.stride(0) == 0:  # the expanded scalar that `nll.sum()` sends back
+            gw = gw[:1]
+        gw = gw.contiguous()
+        with torch.cuda.device(grad.device):
+            rc = _lib.load().b200_ctc_grad_rescale(
+                grad.data_ptr(), _lib.dtype_code(grad.dtype), T, B, V, grad.stride(0), grad.stride(1),
+                gw.data_ptr(), gw.numel(), ctx.hint, ilen.data_ptr(), _stream(grad.device))
+        _lib.check(rc, "b200_ctc_grad_rescale")
+        return grad, None, None, None, None, None, None, None, None
 
 
 def upload_valid_frames(x_host, x_dev, ilen):
@@ -122,22 +190,26 @@ def upload_valid_frames(x_host, x_dev, ilen):
     return nbytes
 
 
-def ctc_nll(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0):
+def ctc_nll(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, grad_scale_hint=1.0, strict=False):
     """Per-utterance negative log-likelihood (B,) fp32 from pre-softmax logits (T,B,V).
 
     targets: 1-D label buffer; utterance b's labels start at tgt_offsets[b] and there are
     olen[b] of them (so both the concatenated form of ``torch.nn.CTCLoss`` and a padded
     (B, Lmax) matrix are accepted without copying).  lmax: host-side bound on olen.
+    grad_scale_hint: the upstream gradient d loss / d nll_b the caller expects (see the module
+    docstring); any other upstream gradient is still honoured, at the price of one more pass over
+    the gradient.  strict: raise ValueError for invalid targets (synchronises; without it such
+    utterances get a NaN loss and NaN gradient rows).
     """
-    return _CTCLossFunction.apply(logits, targets, tgt_offsets, ilen, olen, lmax, blank)
+    return _CTCLossFunction.apply(logits, targets, tgt_offsets, ilen, olen, lmax, blank, grad_scale_hint, strict)
 
 
 def ctc_loss_fwd_bwd(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, grad_weight=None,
                      grad_scale=1.0, grad_out=None, plan=None, nll_out=None, loss_sum_out=None):
     """One fused call: returns (nll (B,), loss_sum (1,), grad (T,B,V) in logits' dtype).
 
-    grad = grad_scale * grad_weight[b] * d nll_b / d logits.  This is the unit of work of
-    ``bench.py`` (CTC loss fwd+bwd) and what a trainer with a known upstream scale uses.
+    grad = grad_scale * grad_weight[b] * d nll_b / d logits.  The raw-ABI form of the unit of
+    work of ``bench.py`` (CTC loss fwd+bwd) for a trainer that knows its upstream scale.
     nll_out (B,) / loss_sum_out (1,) fp32: caller-owned outputs, e.g. a slot of
     ``sharding.LossLedger`` (no allocation and no copy kernel per call).
     """
@@ -159,3 +231,26 @@ def ctc_loss_fwd_bwd(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, gr
             plan.ws_ptr, plan.ws_bytes, _stream(dev))
     _lib.check(rc, "b200_ctc_loss_fwd_bwd")
     return nll, loss_sum, grad
+
+
+def ctc_loss_split(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, grad_weight=None, grad_scale=1.0):
+    """The separate forward / backward entry points (``b200_ctc_loss_forward`` then
+    ``b200_ctc_loss_backward`` on the same workspace: the logits are read twice).  Kept for callers that
+    cannot hold a gradient-sized buffer between forward and backward; the parity tests run it next to the
+    one-pass call.  Returns (nll, grad)."""
+    logits = _prep_logits(logits)
+    plan = _Plan(logits, targets, tgt_offsets, ilen, olen, lmax, blank)
+    dev = logits.device
+    nll = torch.empty(plan.B, dtype=torch.float32, device=dev)
+    grad = _empty_like_strided(logits)
+    gw = None if grad_weight is None else grad_weight.to(device=dev, dtype=torch.float32).contiguous()
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        rc = lib.b200_ctc_loss_forward(*plan.common_args(), nll.data_ptr(), None, plan.ws_ptr, plan.ws_bytes,
+                                       _stream(dev))
+        _lib.check(rc, "b200_ctc_loss_forward")
+        rc = lib.b200_ctc_loss_backward(*plan.common_args(), None if gw is None else gw.data_ptr(), float(grad_scale),
+                                        grad.data_ptr(), grad.stride(0), grad.stride(1), plan.ws_ptr, plan.ws_bytes,
+                                        _stream(dev))
+        _lib.check(rc, "b200_ctc_loss_backward")
+    return nll, grad

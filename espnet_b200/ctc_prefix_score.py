@@ -83,7 +83,7 @@ class CTCPrefixScoreB200(object):
         return torch.cuda.current_stream(self.device).cuda_stream
 
     def _workspace(self, n_bh):
-        need = self._lib.b200_ctc_prefix_work_floats(self.input_length, n_bh)
+        need = self._lib.b200_ctc_prefix_work_floats(self.input_length, n_bh, self.odim)
         if self._work is None or self._work.numel() < need:
             self._work = torch.empty(need, dtype=torch.float32, device=self.device)
         return self._work

@@ -12,6 +12,13 @@ import torch
 
 from .ctc_prefix_score import CTCPrefixScoreB200
 
+try:  # inside an ESPnet installation the scorer IS a BatchPartialScorerInterface: BeamSearch.__init__ asserts
+    # isinstance(v, ScorerInterface) and sorts scorers by isinstance(v, PartialScorerInterface)
+    # (espnet/nets/beam_search.py:80-88); asr_inference.py:115 / recog.py:105 test BatchScorerInterface
+    from espnet.nets.scorer_interface import BatchPartialScorerInterface as _ScorerBase
+except ImportError:  # stand-alone use (this repository's own BatchBeamSearchB200 duck-types its scorers)
+    _ScorerBase = object
+
 
 class _Survivor(object):
     """A hypothesis that survived pruning: (state of the step, parent index, appended label)."""
@@ -36,7 +43,7 @@ class _BeamSurvivors(object):
         return self.parent.numel()
 
 
-class CTCPrefixScorer(object):
+class CTCPrefixScorer(_ScorerBase):
     """Decoder interface wrapper for CTCPrefixScoreB200."""
 
     def __init__(self, ctc: torch.nn.Module, eos: int):
@@ -128,28 +135,3 @@ class CTCPrefixScorer(object):
         presub_score = new_state[1][0, ids.to(new_state[1].device)]
         tscore = (presub_score - prev_score).to(device=x.device, dtype=x.dtype)
         return tscore, (presub_score, (new_state, [int(t) for t in ids]))
-
-
-class LengthBonus(object):
-    """Length bonus in beam search: score 1 for every token (espnet/nets/scorers/length_bonus.py:11-61)."""
-
-    def __init__(self, n_vocab: int):
-        self.n = n_vocab
-
-    def init_state(self, x):
-        return None
-
-    def batch_init_state(self, x):
-        return None
-
-    def select_state(self, state, i, new_id=None):
-        return None if state is None else state[i]
-
-    def final_score(self, state):
-        return 0.0
-
-    def score(self, y, state, x):
-        return torch.tensor([1.0], device=x.device, dtype=x.dtype).expand(self.n), None
-
-    def batch_score(self, ys, states, xs):
-        return torch.tensor([1.0], device=xs.device, dtype=xs.dtype).expand(ys.shape[0], self.n), None

@@ -67,3 +67,52 @@ class LossLedger:
         means = self.buf[: self.interval] / n
         self.buf[self.interval] = self.n_utt
         return means, n
+
+
+class StepLossExchange:
+    """Per-step exchange of (sum of nll, number of utterances) between the ranks, before backward.
+
+    What ``espnet2/train/trainer.py:384-397`` does every iteration: ``stats, weight =
+    recursive_average(stats, weight, distributed)`` (``recursive_op.py:46-53``: one all-reduce for the loss
+    statistic, one for the weight), then ``loss /= weight; loss *= world_size``.  ``step(local_sum)``
+    returns the global mean loss; ``scale()`` the factor B_local * world / sum(B) the local mean loss is
+    multiplied by before ``backward`` (exactly 1 when every rank holds the same number of utterances, which
+    keeps the one-pass gradient written during forward final).
+
+    Transport: `peer` (symmetric memory: every rank's kernel stores its pair straight into the slot ring of
+    all peers over NVLink and waits for theirs -- no NCCL launch on the step path) when
+    ``espnet_b200.peer_exchange`` can set it up, else one NCCL/gloo all-reduce of a 2-float buffer.
+    """
+
+    def __init__(self, device, n_utt, group=None, transport="auto"):
+        self.device, self.group = torch.device(device), group
+        self.n_utt = float(n_utt)
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self.buf = torch.zeros(2, dtype=torch.float32, device=self.device)
+        self.peer = None
+        self.transport = "none" if self.world == 1 else "allreduce"
+        if self.world > 1 and transport in ("auto", "peer") and self.device.type == "cuda":
+            try:
+                from .peer_exchange import PeerSlots
+
+                self.peer = PeerSlots(self.device, group)
+                self.transport = "peer"
+            except Exception as e:  # no symmetric memory on this box / build: the collective still works
+                if transport == "peer":
+                    raise
+                self.why_not_peer = f"{type(e).__name__}: {e}"[:200]
+
+    def step(self, local_sum):
+        """local_sum: this rank's sum of nll (0-dim or 1-element device tensor).  Returns the global mean loss
+        (0-dim tensor); the global utterance count is left in ``self.buf[1]``."""
+        self.buf[0:1].copy_(local_sum.reshape(1))
+        self.buf[1] = self.n_utt
+        if self.peer is not None:
+            self.peer.exchange(self.buf)
+        elif self.world > 1:
+            dist.all_reduce(self.buf, op=dist.ReduceOp.SUM, group=self.group)
+        return self.buf[0] / self.buf[1]
+
+    def scale(self):
+        """n_utt * world / (global utterance count), as a 0-dim device tensor (no host synchronisation)."""
+        return (self.n_utt * self.world) / self.buf[1]

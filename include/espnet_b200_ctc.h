@@ -46,7 +46,7 @@
 extern "C" {
 #endif
 
-#define B200_CTC_ABI_VERSION 1
+#define B200_CTC_ABI_VERSION 2
 
 typedef enum {
   B200_OK = 0,
@@ -149,6 +149,27 @@ int b200_ctc_loss_stream_pass(const void* logits, int dtype,
                               void* grad_logits, int64_t gstride_t, int64_t gstride_b,
                               void* workspace, size_t workspace_bytes, void* stream);
 
+/* Number of utterances of the last _forward / _fwd_bwd call on `workspace` whose targets were
+ * invalid: a label outside [0,V), a label equal to blank, or olen[b] > Lmax.  torch.nn.CTCLoss
+ * raises for such input on the CPU (espnet2/asr/ctc.py:49 calls it); here the kernels clamp the
+ * label / the length so that nothing is read or written out of bounds, give the utterance
+ * nll = NaN and NaN gradient rows, and this call reports the count.  Synchronises `stream`
+ * (one B-int device->host copy): meant for a debug / strict mode, not for every step. */
+int b200_ctc_loss_status(const void* workspace, int64_t T, int64_t B, int64_t V, int64_t Lmax,
+                         int32_t* n_invalid_host, void* stream);
+
+/* grad_logits[t,b,:] *= gout[b] / expected (gout_n == B) or gout[0] / expected (gout_n == 1), in
+ * place, for the autograd backward of a one-pass _fwd_bwd call whose upstream gradient was not
+ * known at forward time: the forward writes expected * d nll_b / d logits, the backward calls this
+ * with the real upstream gradient gout (a DEVICE pointer: no host synchronisation).  Rows whose
+ * ratio is exactly 1 are not touched, so the common case (the trainer's scale equals the hint
+ * given at forward time) costs one launch of a kernel that reads B floats.  ilen (may be NULL)
+ * lets it skip the zero rows past the end of each utterance. */
+int b200_ctc_grad_rescale(void* grad_logits, int dtype, int64_t T, int64_t B, int64_t V,
+                          int64_t gstride_t, int64_t gstride_b,
+                          const float* gout, int64_t gout_n, float expected,
+                          const int64_t* ilen, void* stream);
+
 /* ------------------------------------------------------------------------
  * CTC prefix scoring (CTCPrefixScoreTH)
  * ------------------------------------------------------------------------
@@ -175,8 +196,14 @@ int b200_ctc_prefix_init(float* x, const int64_t* xlens,
  * scores      fp32 (n_bh,V) out: log_psi - s_prev; logzero - s_prev for tokens
  *             not in scoring_ids and for blank; eos gets r_sum[xlens-1].
  * log_psi     fp32 (n_bh,V) out (may alias nothing; needed by _select)
- * work        fp32 scratch of b200_ctc_prefix_work_floats(T, n_bh) floats */
-size_t b200_ctc_prefix_work_floats(int64_t T, int64_t n_bh);
+ * work        fp32 scratch of b200_ctc_prefix_work_floats(T, n_bh, V) floats
+ *
+ * The scores are computed as scaled linear sums (one pass over x for all hypotheses of an
+ * utterance); (hypothesis, token) pairs whose sum falls below 2^-100 of its scale are redone
+ * exactly in log space by a second kernel, so the result never degrades to the sentinel where
+ * the reference returns a finite log-sum-exp.  Any n_hyps >= 1 is accepted (more than 16
+ * hypotheses per utterance are scored in groups of 16). */
+size_t b200_ctc_prefix_work_floats(int64_t T, int64_t n_bh, int64_t V);
 
 int b200_ctc_prefix_score(const float* x, const float* xmax, const int64_t* xlens,
                           int64_t B, int64_t T, int64_t V, int64_t n_hyps,

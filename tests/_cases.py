@@ -27,6 +27,73 @@ def make_loss_case(B, T, V, L, seed, dtype=torch.float32, full=False, forced_rep
     return {"x": x, "ilen": ilen, "olen": olen, "ys": ys}
 
 
+def random_alignment(T, ys, g):
+    """A random valid CTC alignment (T,) of the label sequence ys: every label gets >= 1 frame, repeated labels
+    are separated by >= 1 blank frame, the remaining frames go to random segments (labels or the L+1 blank gaps)."""
+    L = len(ys)
+    need_blank = [0] + [1 if ys[k] == ys[k - 1] else 0 for k in range(1, L)] + [0]   # gap before label k / after the last
+    base = L + sum(need_blank)
+    assert T >= base, (T, base)
+    # segments in order: gap0, y0, gap1, y1, ..., gapL
+    seg_len = []
+    for k in range(L):
+        seg_len += [need_blank[k], 1]
+    seg_len.append(need_blank[L])
+    extra = torch.randint(0, len(seg_len), (T - base,), generator=g).tolist()
+    for e in extra:
+        seg_len[e] += 1
+    a = []
+    for k, n in enumerate(seg_len):
+        a += [0 if k % 2 == 0 else int(ys[k // 2])] * n
+    return torch.tensor(a, dtype=torch.long)
+
+
+def make_logits(kind, B, T, V, ilen, olen, ys, g):
+    """(B,T,V) float32 logits of one of the input distributions the parity tests cover.
+
+      randn      N(0,1): near-uniform posteriors (what bench.py measures)
+      scale8/30  N(0,1) * 8 or * 30: saturated posteriors, log-probs spanning hundreds of nats per frame
+      trained    a converged model: the frame's class on a random valid alignment of the utterance's labels at 0,
+                 every other class at -U(20,40), plus N(0,1) noise
+      mismatch   the same, but the alignment spells a DIFFERENT label sequence than the targets (wrong transcript)
+      level      first half of every utterance `trained`, second half `randn` (an abrupt level change)
+    """
+    if kind == "randn":
+        return torch.randn(B, T, V, generator=g)
+    if kind in ("scale8", "scale30"):
+        return torch.randn(B, T, V, generator=g) * float(kind[5:])
+    x = -(20.0 + 20.0 * torch.rand(B, T, V, generator=g)) + torch.randn(B, T, V, generator=g)
+    for b in range(B):
+        Tb, Lb = int(ilen[b]), int(olen[b])
+        if Tb <= 0:
+            continue
+        yb = ys[b, :Lb].clone()
+        if kind == "mismatch" and Lb > 2:
+            yb = yb[torch.randperm(Lb, generator=g)]            # same labels, different order
+        rep = int((yb[1:] == yb[:-1]).sum()) if Lb > 1 else 0
+        if Tb < Lb + rep:                                       # infeasible anyway: leave the noise
+            continue
+        a = random_alignment(Tb, yb.tolist(), g)
+        x[b, torch.arange(Tb), a] = torch.randn(Tb, generator=g) * 0.1
+    if kind == "level":
+        r = torch.randn(B, T, V, generator=g)
+        for b in range(B):
+            h = int(ilen[b]) // 2
+            x[b, h:] = r[b, h:]
+    return x
+
+
+KINDS = ["randn", "scale8", "scale30", "trained", "mismatch", "level"]
+
+
+def make_loss_case_kind(kind, B, T, V, L, seed, dtype=torch.float32, min_ratio=0.6):
+    """make_loss_case with the logits drawn from `kind` (lengths and labels as in make_loss_case)."""
+    c = make_loss_case(B, T, V, L, seed, dtype=torch.float32, min_ratio=min_ratio)
+    g = torch.Generator().manual_seed(seed + 9000)
+    c["x"] = make_logits(kind, B, T, V, c["ilen"], c["olen"], c["ys"], g).to(dtype)
+    return c
+
+
 def loss_cases():
     """Small cases recorded as golden fixtures (reference outputs stored next to the inputs)."""
     cases = {
@@ -51,12 +118,22 @@ def loss_cases():
     return cases
 
 
-def make_prefix_case(B, T, V, H, seed, nsteps, snum=0):
+def make_prefix_case(B, T, V, H, seed, nsteps, snum=0, kind="randn", min_ratio=0.6, L=None):
+    """log-probs (B,T,V) for prefix scoring.  kind as in make_logits; the `trained` kinds are built around a seeded
+    label sequence per utterance (returned as "labels": the walk tests extend hypotheses along it)."""
     g = torch.Generator().manual_seed(seed)
-    lp = torch.log_softmax(torch.randn(B, T, V, generator=g), dim=-1)
-    xlens = torch.randint(int(0.6 * T), T + 1, (B,), generator=g)
+    labels = None
+    if kind == "randn":
+        x = torch.randn(B, T, V, generator=g)
+    xlens = torch.randint(max(int(min_ratio * T), 2), T + 1, (B,), generator=g)
     xlens[0] = T
-    return {"lp": lp, "xlens": xlens, "H": H, "eos": V - 1, "nsteps": nsteps, "snum": snum, "seed": seed}
+    if kind != "randn":
+        L = L or max(2, int(xlens.min()) // 4)
+        labels = torch.randint(1, V - 1, (B, L), generator=g)
+        x = make_logits(kind, B, T, V, xlens, torch.full((B,), L), labels, g)
+    lp = torch.log_softmax(x, dim=-1)
+    return {"lp": lp, "xlens": xlens, "H": H, "eos": V - 1, "nsteps": nsteps, "snum": snum, "seed": seed,
+            "labels": labels}
 
 
 def prefix_cases():
@@ -88,4 +165,11 @@ def nbest_cases():
         # wide beam against a small vocabulary: fewer live candidates than beam slots at step 0
         "wide_beam": dict(T=30, V=12, L=6, seed=44, beam=10, weights={"ctc": 1.0, "length_bonus": 0.1},
                           pre_beam_score_key=None, pre_beam_ratio=1.5, maxlenratio=0.0),
+        # BPE-sized vocabulary, joint decoding with ctc_weight 0.3 (BASELINE config 3's weights) and a constructed
+        # near-tie (tests/_toy.make_search_input twin): pairs of hypotheses a few 1e-6 apart
+        "v5000_near_tie": dict(T=66, V=5000, L=5, seed=45, beam=10, weights={"decoder": 0.7, "ctc": 0.3, "length_bonus": 0.1},
+                               pre_beam_score_key="full", pre_beam_ratio=1.5, maxlenratio=0.0, twin=3e-5, peak=15.0, tboost=11.0),
+        # the same vocabulary with every token scored by CTC (no pre-beam: recognize_beam_batch's CUDA path)
+        "v5000_full_vocab": dict(T=44, V=5000, L=4, seed=46, beam=8, weights={"decoder": 0.5, "ctc": 0.5},
+                                 pre_beam_score_key=None, pre_beam_ratio=1.5, maxlenratio=0.0, twin=2e-5, peak=15.0, tboost=11.0),
     }

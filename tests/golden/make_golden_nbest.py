@@ -50,8 +50,15 @@ def main():
         for k in nbest[0].scores:
             out[f"{name}_scores_{k}"] = np.array([float(h.scores[k]) for h in nbest], dtype=np.float64)
         out[f"{name}_label"] = y.numpy()
-        # the non-batch BeamSearch of the reference (per-hypothesis numpy CTCPrefixScore): best hypothesis
+        # the non-batch BeamSearch of the reference (per-hypothesis numpy CTCPrefixScore): best hypothesis, and its
+        # whole n-best list
         out[f"{name}_single_best"] = res["single"][0].yseq.numpy()
+        sn = res["single"]
+        sy = np.full((len(sn), max(len(h.yseq) for h in sn)), -1, dtype=np.int64)
+        for i, h in enumerate(sn):
+            sy[i, : len(h.yseq)] = h.yseq.numpy()
+        out[f"{name}_single_yseq"] = sy
+        out[f"{name}_single_score"] = np.array([float(h.score) for h in sn], dtype=np.float64)
         gap = np.diff(out[f"{name}_score"])
         print(name, "n-best", n, "best", ys[0][ys[0] >= 0].tolist(), "label", y.tolist(),
               "min score gap %.3g" % (np.abs(gap).min() if n > 1 else 0.0),

@@ -27,7 +27,7 @@ def test_python_binding_covers_header():
 
 
 def test_abi_version(lib):
-    assert lib.b200_ctc_abi_version() == 1
+    assert lib.b200_ctc_abi_version() == 2
 
 
 def test_workspace_size_monotone(lib):

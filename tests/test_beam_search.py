@@ -8,7 +8,7 @@ import pytest
 import torch
 
 from espnet_b200.batch_beam_search import BatchBeamSearchB200, end_detect
-from espnet_b200.scorers import LengthBonus
+from tests._toy import LengthBonus
 from tests import _cases, _toy
 from tests._util import golden
 
@@ -44,6 +44,63 @@ def _check(name, nbest, cfg):
     assert nbest[0].yseq.tolist() == g[f"{name}_single_best"].tolist()   # and what the non-batch BeamSearch finds
     d = nbest[0].asdict()
     assert isinstance(d["yseq"], list) and isinstance(d["score"], float)
+
+
+def _check_single(name, nbest):
+    """n-best of the reference's NON-batch BeamSearch (numpy CTCPrefixScore per hypothesis)."""
+    g = golden("nbest.npz")
+    ys, score = g[f"{name}_single_yseq"], g[f"{name}_single_score"]
+    assert len(nbest) == ys.shape[0]
+    for i, h in enumerate(nbest):
+        want = ys[i][ys[i] >= 0].tolist()
+        assert h.yseq.tolist() == want, f"{name}: hypothesis {i} differs"
+        assert abs(float(h.score) - score[i]) <= 1e-4 * len(want)
+
+
+def _reference_search(name, cls_name, ctc_scorer, dev):
+    """The REFERENCE's own BeamSearch / BatchBeamSearch (oracle/_ref) around `ctc_scorer`."""
+    from oracle import stage_ref
+
+    if not stage_ref.activate():
+        pytest.skip("oracle/_ref is not staged (python oracle/stage_ref.py in the build container)")
+    import espnet.nets.batch_beam_search as RB
+    import espnet.nets.beam_search as RS
+    from espnet.nets.scorer_interface import BatchScorerInterface
+    from espnet.nets.scorers.length_bonus import LengthBonus as RefLengthBonus
+
+    class RefBigram(_toy.Bigram, BatchScorerInterface):
+        pass
+
+    cfg = _cases.nbest_cases()[name]
+    x, table, _ = _toy.make_search_input(**cfg)
+    V = cfg["V"]
+    scorers = {"decoder": RefBigram(table.to(dev)), "ctc": ctc_scorer, "length_bonus": RefLengthBonus(V)}
+    cls = RB.BatchBeamSearch if cls_name == "BatchBeamSearch" else RS.BeamSearch
+    bs = cls(scorers=scorers, weights=cfg["weights"], beam_size=cfg["beam"], vocab_size=V, sos=V - 1, eos=V - 1,
+             pre_beam_score_key=cfg["pre_beam_score_key"], pre_beam_ratio=cfg["pre_beam_ratio"])
+    assert "ctc" in bs.part_scorers     # passed the isinstance checks of beam_search.py:80-88
+    with torch.no_grad():
+        return bs(x.to(dev), maxlenratio=cfg["maxlenratio"], minlenratio=0.0), cfg
+
+
+def _b200_scorer_class():
+    """espnet_b200.scorers binds to espnet's scorer interfaces at import time: make sure the staged reference was
+    importable when that happened (another test may have imported the module first)."""
+    import importlib
+
+    from oracle import stage_ref
+
+    if not stage_ref.activate():
+        pytest.skip("oracle/_ref is not staged")
+    import espnet_b200.scorers as S
+
+    if S._ScorerBase is object:
+        S = importlib.reload(S)
+    from espnet.nets.scorer_interface import BatchPartialScorerInterface, BatchScorerInterface, PartialScorerInterface, ScorerInterface
+
+    for iface in (ScorerInterface, BatchScorerInterface, PartialScorerInterface, BatchPartialScorerInterface):
+        assert issubclass(S.CTCPrefixScorer, iface)
+    return S.CTCPrefixScorer
 
 
 @pytest.mark.parametrize("name", CASES)
@@ -105,4 +162,65 @@ def test_per_hypothesis_state_path_gives_the_same_nbest():
     name = "joint_full"
     nbest, cfg = _run(name, _PerHypothesis(CTCPrefixScorer(_toy.LogSoftmaxCTC(), cfg_eos(name))),
                       torch.device("cuda"))
+    _check(name, nbest, cfg)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", CASES)
+def test_reference_batch_beam_search_with_the_b200_scorer(name):
+    """The drop-in claim itself: the reference's BatchBeamSearch, unmodified, with espnet_b200's CTCPrefixScorer in
+    place of its own, reproduces the n-best lists it produced with its own scorer (tests/golden/nbest.npz)."""
+    scorer = _b200_scorer_class()(_toy.LogSoftmaxCTC(), cfg_eos(name))
+    nbest, cfg = _reference_search(name, "BatchBeamSearch", scorer, torch.device("cuda"))
+    _check(name, nbest, cfg)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["ctc_only", "joint_full", "joint_decoder", "v5000_near_tie"])
+def test_reference_beam_search_single_hypothesis_path(name):
+    """init_state / score_partial / select_state under the reference's NON-batch BeamSearch, against
+    the n-best that search produced with the reference's numpy CTCPrefixScore."""
+    scorer = _b200_scorer_class()(_toy.LogSoftmaxCTC(), cfg_eos(name))
+    nbest, _ = _reference_search(name, "BeamSearch", scorer, torch.device("cuda"))
+    _check_single(name, nbest)
+
+
+@pytest.mark.gpu
+def test_single_hypothesis_scores_match_numpy_reference():
+    """score_partial against the reference's numpy CTCPrefixScore values (np_first_step_psi of the prefix fixtures)."""
+    from espnet_b200.scorers import CTCPrefixScorer
+
+    for name in ("full", "single", "wide"):
+        g = golden(f"prefix_{name}.npz")
+        lp, xlens, eos = torch.from_numpy(g["lp"]), g["xlens"], int(g["eos"])
+        V = lp.shape[2]
+        x = lp[0, : int(xlens[0])].cuda()
+
+        class Identity(object):
+            def log_softmax(self, h):
+                return h
+
+        sc = CTCPrefixScorer(Identity(), eos)
+        st = sc.init_state(x)
+        ids = torch.arange(V, device="cuda")
+        y = torch.tensor([eos], device="cuda")
+        tscore, _ = sc.score_partial(y, ids, st, x)
+        ref = g["np_first_step_psi"]
+        got = tscore.cpu().numpy()
+        real = ref > -1e9
+        assert (got[~real] < -1e9).all()
+        assert np.abs(got[real] - ref[real]).max() <= 1e-4
+
+
+def test_reference_search_classes_with_oracle_scorer_cpu():
+    """CPU leg of the same harness: the reference's BatchBeamSearch around its OWN scorer reproduces the fixture
+    (the staged tree is the code that made it)."""
+    from oracle import stage_ref
+
+    if not stage_ref.activate():
+        pytest.skip("oracle/_ref is not staged")
+    from espnet.nets.scorers.ctc import CTCPrefixScorer as RefScorer
+
+    name = "joint_full"
+    nbest, cfg = _reference_search(name, "BatchBeamSearch", RefScorer(_toy.LogSoftmaxCTC(), cfg_eos(name)), torch.device("cpu"))
     _check(name, nbest, cfg)

@@ -24,8 +24,8 @@ def _run(x_btv, ilen, olen, ys, grad_scale=None, dtype=None, strided=True, split
     """Returns (nll (B,) float64 numpy, grad (B,T,V) float64 numpy, loss_sum).
 
     split=False: the fused b200_ctc_loss_fwd_bwd call (one pass over the logits when the rows are
-    16-byte aligned); split=True: b200_ctc_loss_forward, then b200_ctc_loss_backward with the
-    upstream gradient, as autograd drives them."""
+    16-byte aligned); split=True: b200_ctc_loss_forward, then b200_ctc_loss_backward on the same
+    workspace (the two-read path)."""
     from espnet_b200 import ctc_loss as CL
 
     B, T, V = x_btv.shape
@@ -34,13 +34,10 @@ def _run(x_btv, ilen, olen, ys, grad_scale=None, dtype=None, strided=True, split
     L = ys.shape[1]
     off = torch.arange(B) * L
     if split:
-        xt = xt.detach().requires_grad_()
-        nll = CL.ctc_nll(xt, ys.cuda().reshape(-1), off, ilen, olen, L)
-        w = torch.full((B,), 1.0 / B if grad_scale is None else grad_scale, device="cuda")
-        nll.backward(w)
+        nll, grad = CL.ctc_loss_split(xt, ys.cuda().reshape(-1), off, ilen, olen, L,
+                                      grad_scale=(1.0 / B if grad_scale is None else grad_scale))
         torch.cuda.synchronize()
-        return (nll.detach().double().cpu().numpy(), xt.grad.transpose(0, 1).double().cpu().numpy(),
-                float(nll.detach().sum().item()))
+        return nll.double().cpu().numpy(), grad.transpose(0, 1).double().cpu().numpy(), float(nll.sum().item())
     nll, ls, grad = CL.ctc_loss_fwd_bwd(xt, ys.cuda().reshape(-1), off, ilen, olen, L,
                                         grad_scale=(1.0 / B if grad_scale is None else grad_scale))
     torch.cuda.synchronize()
@@ -169,6 +166,147 @@ def test_module_forward_backward_like_reference(reduce):
     assert _normrel(h1.grad.double().cpu().numpy(), h2.grad.cpu().numpy()) <= 2e-5
     ga = a.ctc_lo.weight.grad.double().cpu().numpy()
     assert _normrel(ga, r.ctc_lo.weight.grad.cpu().numpy()) <= 2e-5
+
+
+class _Spy(object):
+    """Counts the C-ABI entry points a block of code calls."""
+
+    def __init__(self, lib):
+        self._lib, self.calls = lib, []
+
+    def __getattr__(self, name):
+        fn = getattr(self._lib, name)
+        if name.startswith("b200_ctc_loss") or name.startswith("b200_ctc_grad"):
+            def wrapped(*a, **k):
+                self.calls.append(name)
+                return fn(*a, **k)
+            return wrapped
+        return fn
+
+
+def test_module_call_runs_the_one_pass_kernels(monkeypatch):
+    """CTC(ctc_type="b200").forward + backward = ONE b200_ctc_loss_fwd_bwd (logits read once) and one
+    b200_ctc_grad_rescale that finds nothing to do -- not the forward / backward pair that reads the logits twice."""
+    from espnet_b200 import _lib
+    from espnet_b200.ctc import CTC
+
+    spy = _Spy(_lib.load())
+    monkeypatch.setattr(_lib, "_lib", spy)
+    torch.manual_seed(0)
+    ctc = CTC(16, 8, ctc_type="b200").cuda()
+    hs = torch.randn(3, 20, 8, device="cuda", requires_grad=True)
+    loss = ctc(hs, torch.tensor([20, 15, 18]), torch.randint(1, 16, (3, 4), device="cuda"), torch.tensor([4, 2, 3]))
+    loss.backward()
+    torch.cuda.synchronize()
+    assert spy.calls == ["b200_ctc_loss_workspace_bytes", "b200_ctc_loss_fwd_bwd", "b200_ctc_grad_rescale"]
+    spy.calls.clear()
+    with torch.no_grad():      # evaluation: no gradient is produced
+        ctc(hs, torch.tensor([20, 15, 18]), torch.randint(1, 16, (3, 4), device="cuda"), torch.tensor([4, 2, 3]))
+    assert "b200_ctc_loss_fwd_bwd" not in spy.calls and "b200_ctc_loss_forward" in spy.calls
+
+
+@pytest.mark.parametrize("hint", [1.0, 0.3])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_upstream_gradient_other_than_the_hint(hint, dtype):
+    """loss_fn + backward with upstream gradients that differ from grad_scale_hint (ctc_weight, accum_grad, an AMP
+    loss scale: espnet2/train/trainer.py:394-412): the rescale kernel must reproduce autograd's result."""
+    from espnet_b200.ctc import CTC
+
+    c = _cases.make_loss_case(5, 70, 96, 12, seed=21, dtype=dtype)
+    x, ilen, olen, ys = c["x"], c["ilen"], c["olen"], c["ys"]
+    B = x.shape[0]
+    tg = torch.cat([ys[i, : olen[i]] for i in range(B)])
+    a = CTC(96, 8, ctc_type="b200", grad_scale_hint=hint)
+    r = CTC(96, 8, ctc_type="builtin")
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    for scale in (1.0, 0.3, 1024.0 * 0.3 / 4):
+        xa = x.cuda().transpose(0, 1).detach().requires_grad_()
+        xr = x.cuda().double().transpose(0, 1).detach().requires_grad_()
+        la = a.loss_fn(xa, tg.cuda(), ilen, olen)          # lengths on the host: no synchronisation
+        lr = r.loss_fn(xr, tg.cuda(), ilen, olen)
+        (la * scale).backward()
+        (lr * scale).backward()
+        np.testing.assert_allclose(la.item(), lr.item(), rtol=1e-5)
+        assert _normrel(xa.grad.double().cpu().numpy(), xr.grad.cpu().numpy()) <= tol
+
+
+def test_reduce_false_per_utterance_upstream_gradient():
+    from espnet_b200.ctc import CTC
+
+    c = _cases.make_loss_case(4, 50, 64, 8, seed=22)
+    x, ilen, olen, ys = c["x"], c["ilen"], c["olen"], c["ys"]
+    tg = torch.cat([ys[i, : olen[i]] for i in range(4)])
+    a, r = CTC(64, 8, ctc_type="b200", reduce=False), CTC(64, 8, ctc_type="builtin", reduce=False)
+    xa = x.cuda().transpose(0, 1).detach().requires_grad_()
+    xr = x.cuda().double().transpose(0, 1).detach().requires_grad_()
+    w = torch.tensor([0.5, 2.0, 0.0, 1.0], device="cuda")
+    (a.loss_fn(xa, tg.cuda(), ilen.cuda(), olen.cuda()) * w).sum().backward()
+    (r.loss_fn(xr, tg.cuda(), ilen.cuda(), olen.cuda()) * w.double()).sum().backward()
+    assert _normrel(xa.grad.double().cpu().numpy(), xr.grad.cpu().numpy()) <= 1e-5
+    assert (xa.grad[:, 2] == 0).all()
+
+
+def test_invalid_targets_are_loud():
+    """A label outside [0,V), a blank inside the targets, olen > lmax: torch.nn.CTCLoss raises on the CPU
+    (espnet2/asr/ctc.py:49); here such utterances get nll = NaN and NaN gradient rows, the others are untouched,
+    and strict mode raises."""
+    from espnet_b200 import ctc_loss as CL
+
+    c = _cases.make_loss_case(4, 40, 32, 6, seed=23)
+    x, ilen, olen, ys = c["x"], c["ilen"], c["olen"], c["ys"].clone()
+    good = _run(x, ilen, olen, ys)
+    ys[1, 0] = 32        # out of range
+    ys[2, 1] = 0         # blank as a label
+    nll, grad, _ = _run(x, ilen, olen, ys)
+    assert np.isnan(nll[[1, 2]]).all() and np.isfinite(nll[[0, 3]]).all()
+    assert (nll[[0, 3]] == good[0][[0, 3]]).all() and (grad[[0, 3]] == good[1][[0, 3]]).all()
+    for b in (1, 2):
+        assert np.isnan(grad[b, : int(ilen[b])]).all() and (grad[b, int(ilen[b]):] == 0).all()
+    xt = x.cuda().transpose(0, 1).requires_grad_()
+    off = torch.arange(4) * ys.shape[1]
+    with pytest.raises(ValueError, match="invalid CTC targets"):
+        CL.ctc_nll(xt, ys.cuda().reshape(-1), off, ilen, olen, ys.shape[1], strict=True)
+    # olen beyond the lmax the workspace was sized for: clamped and flagged, nothing is written out of bounds
+    ys = c["ys"]
+    too_long = olen.clone()
+    too_long[0] = 9
+    nll = CL.ctc_nll(xt, ys.cuda().reshape(-1), off, ilen, too_long, 6)
+    assert torch.isnan(nll[0]) and torch.isfinite(nll[1:]).all()
+    with pytest.raises(ValueError):
+        CL.ctc_nll(xt, ys.cuda().reshape(-1), off, ilen, too_long, 6, strict=True)
+    CL.ctc_nll(xt, ys.cuda().reshape(-1), off, ilen, olen, 6, strict=True)   # valid input passes
+
+
+def test_espnet1_module_gradients_match_builtin():
+    from espnet_b200.ctc import CTCEspnet1
+
+    torch.manual_seed(2)
+    B, T, D, V = 3, 25, 8, 9
+    a = CTCEspnet1(V, D, 0.0, ctc_type="b200").cuda()
+    r = CTCEspnet1(V, D, 0.0, ctc_type="builtin").cuda().double()
+    r.load_state_dict({k: v.double() for k, v in a.state_dict().items()})
+    hs = torch.randn(B, T, D, device="cuda")
+    ys_pad = torch.tensor([[1, 2, 3, -1], [4, 4, -1, -1], [5, 6, 7, 8]], device="cuda")
+    h1, h2 = hs.clone().requires_grad_(), hs.double().requires_grad_()
+    a(h1, [25, 20, 18], ys_pad).backward()
+    r(h2, [25, 20, 18], ys_pad).backward()
+    assert _normrel(h1.grad.double().cpu().numpy(), h2.grad.cpu().numpy()) <= 2e-5
+    assert _normrel(a.ctc_lo.weight.grad.double().cpu().numpy(), r.ctc_lo.weight.grad.cpu().numpy()) <= 2e-5
+
+
+def test_forced_align_builtin_and_b200_agree_with_reference_fixture():
+    from espnet_b200.ctc import CTCEspnet1
+
+    g = golden("viterbi.npz")
+    for k in range(3):
+        h, y, want = torch.from_numpy(g[f"h_{k}"]), torch.from_numpy(g[f"y_{k}"]), g[f"align_{k}"].tolist()
+        V = h.shape[1]
+        for kind, dev in (("b200", "cuda"), ("builtin", "cuda"), ("builtin", "cpu")):
+            ctc = CTCEspnet1(V, V, 0.0, ctc_type=kind).to(dev)
+            with torch.no_grad():
+                ctc.ctc_lo.weight.copy_(torch.eye(V))
+                ctc.ctc_lo.bias.zero_()
+                assert [int(t) for t in ctc.forced_align(h.to(dev).unsqueeze(0), y)] == want
 
 
 def test_espnet1_module_matches_builtin():

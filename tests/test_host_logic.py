@@ -68,3 +68,41 @@ def test_empty_like_strided_matches_ctc_lo_view():
     assert g.shape == x.shape and g.stride() == x.stride()
     y = torch.empty(5, 3, 8)
     assert _empty_like_strided(y).stride() == y.stride()
+
+
+def test_forced_align_of_the_builtin_type_runs_on_the_host():
+    """ctc_type="builtin" keeps the reference's numpy forced_align (pytorch_backend/ctc.py:153-216)."""
+    from espnet_b200.ctc import CTCEspnet1
+
+    g = golden("viterbi.npz")
+    for k in range(3):
+        h, y = torch.from_numpy(g[f"h_{k}"]), torch.from_numpy(g[f"y_{k}"])
+        V = h.shape[1]
+        ctc = CTCEspnet1(V, V, 0.0, ctc_type="builtin")
+        with torch.no_grad():
+            ctc.ctc_lo.weight.copy_(torch.eye(V))
+            ctc.ctc_lo.bias.zero_()
+            assert [int(t) for t in ctc.forced_align(h.unsqueeze(0), y)] == g[f"align_{k}"].tolist()
+
+
+def test_scorer_derives_from_the_reference_interfaces_when_they_are_importable():
+    import importlib
+
+    from oracle import stage_ref
+
+    if not stage_ref.activate():
+        pytest.skip("oracle/_ref is not staged")
+    import espnet_b200.scorers as S
+
+    S = importlib.reload(S)
+    from espnet.nets.scorer_interface import BatchPartialScorerInterface, ScorerInterface
+
+    assert issubclass(S.CTCPrefixScorer, BatchPartialScorerInterface) and issubclass(S.CTCPrefixScorer, ScorerInterface)
+
+
+def test_pack_labels_host_and_mixed_inputs():
+    from espnet_b200.ctc_loss import pack_labels
+
+    out = pack_labels([3, 4, 5], torch.tensor([0, 2]), torch.tensor([7, 9], dtype=torch.int32), [2, 1], torch.device("cpu"))
+    assert [o.tolist() for o in out] == [[3, 4, 5], [0, 2], [7, 9], [2, 1]]
+    assert all(o.dtype == torch.int64 for o in out)
