@@ -20,11 +20,11 @@ SIGNATURES = {
     "b200_last_error": (ctypes.c_char_p, []),
     "b200_ctc_loss_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64]),
     "b200_ctc_loss_forward": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp,
-                                     _i64, _int, _vp, _vp, _vp, _sz, _vp]),
+                                     _i64, _int, _vp, _vp, _f32, _vp, _sz, _vp]),
     "b200_ctc_loss_backward": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp,
                                       _i64, _int, _vp, _f32, _vp, _i64, _i64, _vp, _sz, _vp]),
     "b200_ctc_loss_fwd_bwd": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp,
-                                     _i64, _int, _vp, _f32, _vp, _vp, _vp, _i64, _i64, _vp, _sz, _vp]),
+                                     _i64, _int, _vp, _f32, _vp, _vp, _f32, _vp, _i64, _i64, _vp, _sz, _vp]),
     "b200_ctc_loss_stream_pass": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp,
                                          _i64, _int, _vp, _f32, _vp, _i64, _i64, _vp, _sz, _vp]),
     "b200_ctc_prefix_init": (_int, [_vp, _vp, _i64, _i64, _i64, _int, _vp, _vp, _vp]),

@@ -3,6 +3,9 @@
 
 #include <string.h>
 
+#include <mutex>
+#include <vector>
+
 namespace b200 {
 
 static thread_local char g_err[512] = {0};
@@ -44,6 +47,56 @@ int max_smem_optin() {
     g_smem[dev] = n;
   }
   return g_smem[dev];
+}
+
+namespace {
+struct AttrKey {
+  const void* kern;
+  int dev, a, b;
+  bool operator==(const AttrKey& o) const { return kern == o.kern && dev == o.dev && a == o.a && b == o.b; }
+};
+struct AttrEntry {
+  AttrKey key;
+  int value;
+};
+// a handful of kernels x devices: a linear scan under a mutex is cheaper than the driver call it saves
+std::mutex g_attr_mu;
+std::vector<AttrEntry> g_smem_set, g_occ;
+}  // namespace
+
+cudaError_t set_max_smem_cached(const void* kern, int bytes) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  {
+    std::lock_guard<std::mutex> lk(g_attr_mu);
+    for (const AttrEntry& x : g_smem_set)
+      if (x.key.kern == kern && x.key.dev == dev && x.value >= bytes) return cudaSuccess;
+  }
+  e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lk(g_attr_mu);
+  for (AttrEntry& x : g_smem_set)
+    if (x.key.kern == kern && x.key.dev == dev) { x.value = bytes; return cudaSuccess; }
+  g_smem_set.push_back(AttrEntry{AttrKey{kern, dev, 0, 0}, bytes});
+  return cudaSuccess;
+}
+
+cudaError_t max_blocks_per_sm_cached(const void* kern, int threads, size_t smem, int* out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const AttrKey key{kern, dev, threads, (int)smem};
+  {
+    std::lock_guard<std::mutex> lk(g_attr_mu);
+    for (const AttrEntry& x : g_occ)
+      if (x.key == key) { *out = x.value; return cudaSuccess; }
+  }
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(out, kern, threads, smem);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lk(g_attr_mu);
+  g_occ.push_back(AttrEntry{key, *out});
+  return cudaSuccess;
 }
 
 }  // namespace b200

@@ -19,6 +19,10 @@ void set_error(const char* fmt, ...);
 int cuda_fail(cudaError_t e, const char* what);
 int num_sms();        // SM count of the current device (cached per device)
 int max_smem_optin(); // max dynamic shared memory per block (opt-in)
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) / the occupancy query, remembered per (kernel, device, size):
+// both cost microseconds of host time, and a training step launches the same kernels with the same sizes forever
+cudaError_t set_max_smem_cached(const void* kern, int bytes);
+cudaError_t max_blocks_per_sm_cached(const void* kern, int threads, size_t smem, int* out);
 
 #define B200_CHECK_ARG(cond, code, ...)            \
   do {                                             \

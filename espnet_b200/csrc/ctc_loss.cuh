@@ -98,7 +98,8 @@ struct LossParams {
   float* nll;
   LossWs ws;
   int b0, b1;     // utterance range handled by this launch
-  float* loss_sum; // sum_b nll[b], written by the sweep CTA that finishes last (may be NULL)
+  float* loss_sum; // loss_scale * sum_b nll[b], written by the sweep CTA that finishes last (may be NULL)
+  float loss_scale;
   int prep_after_stream;  // fused call: the prep kernel is a programmatic dependent of the stream kernel
 };
 

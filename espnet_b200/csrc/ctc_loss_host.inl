@@ -119,7 +119,7 @@ static LossParams make_params(const void* logits, int64_t T, int64_t B, int64_t 
 
 static int launch_prep(const LossParams& p, cudaStream_t st);
 
-static int run_forward(LossParams p, int dtype, float* loss_sum, cudaStream_t st) {
+static int run_forward(LossParams p, int dtype, float* loss_sum, float loss_scale, cudaStream_t st) {
   const int es = elem_size(dtype);
   RowsCfg cfg;
   int rc = plan_rows(p, false, rows_vec_ok(p.logits, p.V, p.stride_t, p.stride_b, es), &cfg);
@@ -130,6 +130,7 @@ static int run_forward(LossParams p, int dtype, float* loss_sum, cudaStream_t st
   rc = launch_rows<false>(p, dtype, cfg, st);
   if (rc) return rc;
   p.loss_sum = loss_sum;  // written by the sweep CTA that finishes last
+  p.loss_scale = loss_scale;
   rc = launch_sweep(p, st);
   if (rc) return rc;
   // occupancies for the backward pass (cheap, and keeps _backward a pure stream)
@@ -147,7 +148,7 @@ static int launch_prep(const LossParams& p, cudaStream_t st) {
 
 // One pass over the logits (stream), the two lattice sweeps, and the column patch.
 // Returns false in *done when the shape needs the general three-pass path.
-static int run_fused(LossParams p, int dtype, float* loss_sum, cudaStream_t st, bool* done,
+static int run_fused(LossParams p, int dtype, float* loss_sum, float loss_scale, cudaStream_t st, bool* done,
                      bool stream_only = false) {
   *done = false;
   const int es = elem_size(dtype);
@@ -156,6 +157,7 @@ static int run_fused(LossParams p, int dtype, float* loss_sum, cudaStream_t st, 
       !rows_vec_ok(p.grad, p.V, p.gstride_t, p.gstride_b, es) || !plan_stream(p, es, &sc))
     return B200_OK;
   p.loss_sum = loss_sum;  // (the prep kernel zeroes the workspace counters)
+  p.loss_scale = loss_scale;
   // The stream kernel reads the int64 labels itself, so the 6 us label-prep kernel (int32 labels, duplicate
   // codes, length ranking, workspace counters: inputs of the sweeps and of the patch) is launched AFTER it
   // as a programmatic dependent and runs under it.  stream -> prep -> sweeps -> patch are all chained by
@@ -197,15 +199,15 @@ extern "C" size_t b200_ctc_loss_workspace_bytes(int64_t T, int64_t B, int64_t V,
 extern "C" int b200_ctc_loss_forward(const void* logits, int dtype, int64_t T, int64_t B, int64_t V,
                                      int64_t stride_t, int64_t stride_b, const int64_t* targets,
                                      const int64_t* tgt_offsets, const int64_t* ilen, const int64_t* olen,
-                                     int64_t Lmax, int blank, float* nll, float* loss_sum, void* workspace,
-                                     size_t workspace_bytes, void* stream) {
+                                     int64_t Lmax, int blank, float* nll, float* loss_sum, float loss_scale,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
   int rc = check_common(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
                         blank, workspace, workspace_bytes);
   if (rc) return rc;
   B200_CHECK_ARG(nll != nullptr, B200_ERR_INVALID_ARGUMENT, "nll is null");
   LossParams p = make_params(logits, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
                              blank, nll, workspace);
-  return run_forward(p, dtype, loss_sum, (cudaStream_t)stream);
+  return run_forward(p, dtype, loss_sum, loss_scale, (cudaStream_t)stream);
 }
 
 extern "C" int b200_ctc_loss_backward(const void* logits, int dtype, int64_t T, int64_t B, int64_t V,
@@ -231,8 +233,9 @@ extern "C" int b200_ctc_loss_fwd_bwd(const void* logits, int dtype, int64_t T, i
                                      int64_t stride_t, int64_t stride_b, const int64_t* targets,
                                      const int64_t* tgt_offsets, const int64_t* ilen, const int64_t* olen,
                                      int64_t Lmax, int blank, const float* grad_weight, float grad_scale,
-                                     float* nll, float* loss_sum, void* grad_logits, int64_t gstride_t,
-                                     int64_t gstride_b, void* workspace, size_t workspace_bytes, void* stream) {
+                                     float* nll, float* loss_sum, float loss_scale, void* grad_logits,
+                                     int64_t gstride_t, int64_t gstride_b, void* workspace, size_t workspace_bytes,
+                                     void* stream) {
   int rc = check_common(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen, Lmax,
                         blank, workspace, workspace_bytes);
   if (rc) return rc;
@@ -246,12 +249,12 @@ extern "C" int b200_ctc_loss_fwd_bwd(const void* logits, int dtype, int64_t T, i
     p.gstride_t = gstride_t; p.gstride_b = gstride_b;
     p.grad_weight = grad_weight; p.grad_scale = grad_scale;
     bool done = false;
-    rc = run_fused(p, dtype, loss_sum, (cudaStream_t)stream, &done);
+    rc = run_fused(p, dtype, loss_sum, loss_scale, (cudaStream_t)stream, &done);
     if (rc || done) return rc;
   }
   // general shapes: three passes (rowstats, lattice, gradient)
   rc = b200_ctc_loss_forward(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen,
-                             Lmax, blank, nll, loss_sum, workspace, workspace_bytes, stream);
+                             Lmax, blank, nll, loss_sum, loss_scale, workspace, workspace_bytes, stream);
   if (rc) return rc;
   return b200_ctc_loss_backward(logits, dtype, T, B, V, stride_t, stride_b, targets, tgt_offsets, ilen, olen,
                                 Lmax, blank, grad_weight, grad_scale, grad_logits, gstride_t, gstride_b,
@@ -274,7 +277,7 @@ extern "C" int b200_ctc_loss_stream_pass(const void* logits, int dtype, int64_t 
   p.gstride_t = gstride_t; p.gstride_b = gstride_b;
   p.grad_weight = grad_weight; p.grad_scale = grad_scale;
   bool done = false;
-  rc = run_fused(p, dtype, nullptr, (cudaStream_t)stream, &done, true);
+  rc = run_fused(p, dtype, nullptr, 1.0f, (cudaStream_t)stream, &done, true);
   if (rc) return rc;
   B200_CHECK_ARG(done, B200_ERR_UNSUPPORTED_SHAPE, "this shape runs on the three-pass path (no one-pass stream stage)");
   return B200_OK;

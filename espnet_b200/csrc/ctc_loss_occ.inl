@@ -352,10 +352,10 @@ static int launch_occ_nj(const LossParams& p, cudaStream_t st) {
   const OccPlan pl = plan_occ(p.ws.Kp);
   B200_CHECK_ARG(pl.warps > 0, B200_ERR_UNSUPPORTED_SHAPE, "Lmax=%lld: a lattice row does not fit in shared memory",
                  (long long)p.Lmax);
-  B200_CUDA(cudaFuncSetAttribute(ctc_occ_kernel<T, PATCH, NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+  B200_CUDA(set_max_smem_cached((const void*)ctc_occ_kernel<T, PATCH, NJ>, (int)pl.smem));
   const int64_t units = (int64_t)(p.b1 - p.b0) * p.T;  // rows, at least one per warp
   int per_sm = 1;
-  B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ctc_occ_kernel<T, PATCH, NJ>, pl.warps * 32, pl.smem));
+  B200_CUDA(max_blocks_per_sm_cached((const void*)ctc_occ_kernel<T, PATCH, NJ>, pl.warps * 32, pl.smem, &per_sm));
   if (per_sm < 1) per_sm = 1;
   int64_t g = (units + pl.warps - 1) / pl.warps;
   const int64_t cap = (int64_t)num_sms() * per_sm;  // persistent: every CTA resident

@@ -359,7 +359,7 @@ static int launch_stream_t(const LossParams& p, const StreamCfg& c, cudaStream_t
   int64_t g = num_sms();
   if (g > nrows) g = nrows;
   auto go = [&](auto kern) -> int {
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem));
+    B200_CUDA(set_max_smem_cached((const void*)kern, c.smem));
     B200_CUDA(launch_kernel(kern, dim3((unsigned)g), dim3((kStreamWarps + 1) * 32), (size_t)c.smem, st,
                             false, p, c.nslots, c.slot_bytes));
     return B200_OK;

@@ -62,7 +62,7 @@ __device__ __forceinline__ void sweep_finish_nll(const LossParams& p, int b, flo
     __threadfence();
     float s = 0.f;
     for (int o = p.b0; o < p.b1; ++o) s += ld_cg_f32(p.nll + o);
-    *p.loss_sum = s;
+    *p.loss_sum = s * p.loss_scale;
   }
 }
 
@@ -705,7 +705,7 @@ static int launch_sweep_t(const LossParams& p, int threads, cudaStream_t st, boo
   // up first.)  Asking for more than half of the shared memory caps residency at one CTA per SM.
   if (2 * (p.b1 - p.b0) <= num_sms() && smem < 116 * 1024) smem = 116 * 1024;
   auto kern = ctc_sweep_kernel<CHF, MAXT>;
-  if (smem > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (smem > 48 * 1024) B200_CUDA(set_max_smem_cached((const void*)kern, (int)smem));
   B200_CUDA(launch_kernel(kern, dim3((unsigned)(p.b1 - p.b0), 2), dim3(threads), smem, st, pdl, p));
   return B200_OK;
 }
@@ -717,7 +717,7 @@ static int launch_sweep_staged(const LossParams& p, int threads, cudaStream_t st
   // one latency chain per SM whenever the grid fits that way (see launch_sweep_t)
   if (2 * (p.b1 - p.b0) <= num_sms() && smem < 116 * 1024) smem = 116 * 1024;
   auto kern = ctc_sweep_staged_kernel;
-  if (smem > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (smem > 48 * 1024) B200_CUDA(set_max_smem_cached((const void*)kern, (int)smem));
   B200_CUDA(launch_kernel(kern, dim3((unsigned)(p.b1 - p.b0), 2), dim3(threads), smem, st, pdl, p));
   return B200_OK;
 }

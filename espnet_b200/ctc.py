@@ -22,20 +22,25 @@ def _b200_loss(th_pred, targets, tgt_offsets, th_ilen, th_olen, lmax, reduce, hi
     """(T,B,V) pre-softmax logits -> CTCLoss(sum|none)(log_softmax(.)) / B.
 
     The one-pass kernels write the gradient during the forward call, scaled by the upstream gradient they
-    expect for nll_b: `hint` (what the trainer multiplies this loss by: ctc_weight / accum_grad x the AMP loss
-    scale; 1.0 for a bare ``loss.backward()``) divided by B.  Any other upstream gradient is honoured in
-    backward by one more pass over the gradient."""
+    expect: `hint` (what the trainer multiplies this loss by: ctc_weight / accum_grad x the AMP loss scale;
+    1.0 for a bare ``loss.backward()``).  Any other upstream gradient is honoured in backward by one more
+    pass over the gradient.  The reduced loss (sum over utterances, / B) comes out of the lattice kernel
+    itself."""
     B = th_pred.size(1)
+    if reduce:
+        return ctc_nll(th_pred, targets, tgt_offsets, th_ilen, th_olen, lmax, blank=0, grad_scale_hint=hint,
+                       strict=strict, reduce_scale=1.0 / B)
     nll = ctc_nll(th_pred, targets, tgt_offsets, th_ilen, th_olen, lmax, blank=0, grad_scale_hint=hint / B,
                   strict=strict)
-    loss = nll.sum() if reduce else nll
-    return loss / B
+    return nll / B
 
 
 def _host_max(lens):
     """max of a length vector without touching the device when the lengths are host values."""
     if torch.is_tensor(lens):
-        return int(lens.max()) if lens.numel() else 0
+        if lens.numel() == 0:
+            return 0
+        return int(lens.numpy().max()) if not lens.is_cuda else int(lens.max())
     return int(max(lens)) if len(lens) else 0
 
 
@@ -113,11 +118,8 @@ class CTC(torch.nn.Module):
         """th_pred (T,B,V) logits, th_target 1-D concatenated labels (espnet2/asr/ctc.py:46)."""
         if self.ctc_type == "b200":
             # (lengths on the host, as espnet1 passes them, keep this free of device synchronisation)
-            lmax = _host_max(th_olen)
-            olen = torch.as_tensor(th_olen)
-            off = torch.cumsum(olen, 0) - olen
-            return _b200_loss(th_pred, th_target, off, th_ilen, olen, lmax, self.reduce, self.grad_scale_hint,
-                              self.strict_targets)
+            return _b200_loss(th_pred, th_target, None, th_ilen, th_olen, _host_max(th_olen), self.reduce,
+                              self.grad_scale_hint, self.strict_targets)
         elif self.ctc_type == "builtin":
             th_pred = th_pred.log_softmax(2)
             loss = self.ctc_loss(th_pred, th_target, th_ilen, th_olen)
@@ -210,11 +212,8 @@ class CTCEspnet1(torch.nn.Module):
 
     def loss_fn(self, th_pred, th_target, th_ilen, th_olen):
         if self.ctc_type == "b200":
-            lmax = _host_max(th_olen)
-            olen = torch.as_tensor(th_olen)
-            off = torch.cumsum(olen, 0) - olen
-            return _b200_loss(th_pred, th_target, off, th_ilen, olen, lmax, self.reduce, self.grad_scale_hint,
-                              self.strict_targets)
+            return _b200_loss(th_pred, th_target, None, th_ilen, th_olen, _host_max(th_olen), self.reduce,
+                              self.grad_scale_hint, self.strict_targets)
         elif self.ctc_type == "builtin":
             th_pred = th_pred.log_softmax(2)
             with torch.backends.cudnn.flags(deterministic=True):

@@ -16,6 +16,7 @@ compares the real upstream gradient with the expectation ON THE DEVICE (no host 
 and touches only the rows whose ratio is not exactly 1.  When the trainer's scale equals the hint,
 ``loss.backward()`` costs one launch of a kernel that reads B floats.
 """
+import numpy as np
 import torch
 
 from . import _lib
@@ -47,28 +48,90 @@ def _empty_like_strided(x):
     return torch.empty((T, B, V), dtype=x.dtype, device=x.device)
 
 
+class _PinnedRing(object):
+    """A few pinned host buffers per device for the label side of a call, reused round-robin.  A slot is reused
+    only after the copy that last read it has completed (one CUDA event per slot, normally long done)."""
+
+    SLOTS = 8
+
+    def __init__(self):
+        self.buf, self.np, self.ev, self.i = [None] * self.SLOTS, [None] * self.SLOTS, [None] * self.SLOTS, 0
+
+    def take(self, n):
+        k = self.i
+        self.i = (k + 1) % self.SLOTS
+        if self.ev[k] is not None:
+            self.ev[k].synchronize()
+        if self.buf[k] is None or self.buf[k].numel() < n:
+            self.buf[k] = torch.empty(max(n, 16384), dtype=torch.int64, pin_memory=True)
+            self.np[k] = self.buf[k].numpy()
+        return k
+
+    def sent(self, k):
+        if self.ev[k] is None:
+            self.ev[k] = torch.cuda.Event()
+        self.ev[k].record()
+
+
+_rings = {}
+
+
+def _host_np(x):
+    """int64 numpy view / copy of a host-side length or label vector (tensor, list, numpy)."""
+    if torch.is_tensor(x):
+        x = x.detach().numpy()
+    return np.asarray(x).reshape(-1)
+
+
 def pack_labels(targets, tgt_offsets, ilen, olen, device):
-    """ONE host->device copy for the label side of a call: [targets | tgt_offsets | ilen | olen] as int64
-    in one pinned staging buffer (a step otherwise issues four small pageable copies, each a host
-    synchronisation).  Inputs that already live on `device` are used as they are.
-    Returns (targets, tgt_offsets, ilen, olen) as int64 device tensors."""
+    """The label side of a call as int64 device memory: (targets, tgt_offsets, ilen, olen) tensors.
+
+    Everything that lives on the host travels in ONE pinned staging buffer and ONE asynchronous copy (a step
+    otherwise issues four small pageable copies, each a host synchronisation); inputs that already live on
+    `device` are used as they are.  tgt_offsets=None means "targets are concatenated": the offsets are the
+    exclusive prefix sum of olen (computed on the host when olen is there)."""
+    device = torch.device(device)
     parts = [targets, tgt_offsets, ilen, olen]
-    parts = [p if torch.is_tensor(p) else torch.as_tensor(p) for p in parts]
-    host = [k for k, p in enumerate(parts) if not p.is_cuda]
-    out = list(parts)
+    on_dev = [torch.is_tensor(p) and p.is_cuda for p in parts]
+    if tgt_offsets is None:
+        if on_dev[3]:
+            o64 = olen.to(torch.int64)
+            parts[1], on_dev[1] = torch.cumsum(o64, 0) - o64, True
+        else:
+            o = _host_np(olen).astype(np.int64, copy=False)
+            parts[1] = np.cumsum(o) - o
+    out = [None] * 4
+    host = [k for k in range(4) if not on_dev[k]]
+    if host and device.type != "cuda":   # (CPU tensors: only the argument plumbing is exercised, by the CPU tests)
+        for k in host:
+            out[k] = torch.from_numpy(np.ascontiguousarray(_host_np(parts[k]), dtype=np.int64))
+        host = []
     if host:
-        sizes = [parts[k].numel() for k in host]
-        stage = torch.empty(sum(sizes), dtype=torch.int64, pin_memory=torch.device(device).type == "cuda")
+        arrs = [_host_np(parts[k]) for k in host]
+        n = sum(a.size for a in arrs)
+        ring = _rings.get(device)
+        if ring is None:
+            ring = _rings[device] = _PinnedRing()
+        slot = ring.take(n)
+        stage = ring.np[slot]
         o = 0
-        for k, n in zip(host, sizes):
-            stage[o:o + n].copy_(parts[k].reshape(-1))
-            o += n
-        dev = stage.to(device, non_blocking=True)
+        for a in arrs:
+            stage[o:o + a.size] = a
+            o += a.size
+        dev = torch.empty(n, dtype=torch.int64, device=device)
+        dev.copy_(ring.buf[slot][:n], non_blocking=True)
+        ring.sent(slot)
         o = 0
-        for k, n in zip(host, sizes):
-            out[k] = dev[o:o + n]
-            o += n
-    return tuple(_as_i64(p, device) for p in out)
+        for k, a in zip(host, arrs):
+            out[k] = dev[o:o + a.size]
+            o += a.size
+    for k in range(4):
+        if out[k] is None:
+            out[k] = parts[k].to(device=device, dtype=torch.int64).contiguous()
+    return tuple(out)
+
+
+_ws_bytes_cache = {}
 
 
 class _Plan(object):
@@ -84,8 +147,10 @@ class _Plan(object):
         self.lmax = int(lmax)
         self.blank = int(blank)
         self.dtype = _lib.dtype_code(logits.dtype)
-        lib = _lib.load()
-        nbytes = lib.b200_ctc_loss_workspace_bytes(self.T, self.B, self.V, self.lmax)
+        key = (self.T, self.B, self.V, self.lmax)
+        nbytes = _ws_bytes_cache.get(key)
+        if nbytes is None:
+            nbytes = _ws_bytes_cache[key] = _lib.load().b200_ctc_loss_workspace_bytes(*key)
         self.workspace = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
         base = self.workspace.data_ptr()
         self.ws_ptr = (base + 255) // 256 * 256
@@ -114,6 +179,23 @@ def _stream(device):
     return torch.cuda.current_stream(device).cuda_stream
 
 
+class _on(object):
+    """`with _on(device)`: torch.cuda.device(device) only when it is not already the current device."""
+
+    __slots__ = ("guard",)
+
+    def __init__(self, device):
+        self.guard = None if torch.cuda.current_device() == device.index else torch.cuda.device(device)
+
+    def __enter__(self):
+        if self.guard is not None:
+            self.guard.__enter__()
+
+    def __exit__(self, *a):
+        if self.guard is not None:
+            self.guard.__exit__(*a)
+
+
 def _check_strict(plan):
     n = plan.invalid_utterances()
     if n:
@@ -122,52 +204,63 @@ def _check_strict(plan):
 
 
 class _CTCLossFunction(torch.autograd.Function):
-    """nll (B,) fp32 = -log p(y_b | x_b); backward gives d/d logits.
+    """reduce_scale is None:  nll (B,) fp32 = -log p(y_b | x_b);
+    reduce_scale = s:         the 0-dim loss s * sum_b nll_b, summed inside the lattice kernel (CTC.loss_fn's
+                              CTCLoss(reduction="sum") / B is s = 1/B: no reduction or division kernel follows).
+    backward gives d/d logits.
 
-    With a gradient expected for the logits, forward runs the one-pass fused call with
-    grad_scale = `hint` and keeps the finished gradient; backward rescales it on the device where
-    the upstream gradient differs from the hint.  Without one (evaluation), forward only runs
-    the row statistics and the lattice sweeps."""
+    With a gradient expected for the logits, forward runs the one-pass fused call with the EXPECTED upstream
+    gradient `hint` and keeps the finished gradient; backward rescales it on the device where the real upstream
+    gradient differs.  Without one (evaluation), forward only runs the row statistics and the lattice sweeps."""
 
     @staticmethod
-    def forward(ctx, logits, targets, tgt_offsets, ilen, olen, lmax, blank, hint, strict):
+    def forward(ctx, logits, targets, tgt_offsets, ilen, olen, lmax, blank, hint, strict, reduce_scale):
         logits = _prep_logits(logits.detach())
         plan = _Plan(logits, targets, tgt_offsets, ilen, olen, lmax, blank)
         dev = logits.device
         nll = torch.empty(plan.B, dtype=torch.float32, device=dev)
+        reduced = reduce_scale is not None
+        loss = torch.empty((), dtype=torch.float32, device=dev) if reduced else None
+        loss_ptr, s = (loss.data_ptr(), float(reduce_scale)) if reduced else (None, 1.0)
         ctx.hint = float(hint)
+        lib = _lib.load()
         if ctx.needs_input_grad[0]:
             grad = _empty_like_strided(logits)
-            with torch.cuda.device(dev):
-                rc = _lib.load().b200_ctc_loss_fwd_bwd(
-                    *plan.common_args(), None, ctx.hint, nll.data_ptr(), None, grad.data_ptr(),
+            with _on(dev):
+                rc = lib.b200_ctc_loss_fwd_bwd(
+                    *plan.common_args(), None, ctx.hint * s, nll.data_ptr(), loss_ptr, s, grad.data_ptr(),
                     grad.stride(0), grad.stride(1), plan.ws_ptr, plan.ws_bytes, _stream(dev))
             _lib.check(rc, "b200_ctc_loss_fwd_bwd")
             ctx.save_for_backward(grad, plan.ilen)
         else:
-            with torch.cuda.device(dev):
-                rc = _lib.load().b200_ctc_loss_forward(
-                    *plan.common_args(), nll.data_ptr(), None, plan.ws_ptr, plan.ws_bytes, _stream(dev))
+            with _on(dev):
+                rc = lib.b200_ctc_loss_forward(
+                    *plan.common_args(), nll.data_ptr(), loss_ptr, s, plan.ws_ptr, plan.ws_bytes, _stream(dev))
             _lib.check(rc, "b200_ctc_loss_forward")
         if strict:
             _check_strict(plan)
         # the workspace goes back to the allocator here: reuse is ordered on this stream
-        return nll
+        return loss if reduced else nll
 
     @staticmethod
-    def backward(ctx, grad_nll):
+    def backward(ctx, gout):
         grad, ilen = ctx.saved_tensors
         T, B, V = grad.shape
-        gw = grad_nll.to(dtype=torch.float32).reshape(-1)
-        if gw.numel() > 1 and gw.stride(0) == 0:  # the expanded scalar that `nll.sum()` sends back
-            gw = gw[:1]
-        gw = gw.contiguous()
-        with torch.cuda.device(grad.device):
+        gw = gout
+        if gw.dtype != torch.float32:
+            gw = gw.to(dtype=torch.float32)
+        if gw.dim() != 0:
+            gw = gw.reshape(-1)
+            if gw.numel() > 1 and gw.stride(0) == 0:  # the expanded scalar that `nll.sum()` sends back
+                gw = gw[:1]
+            gw = gw.contiguous()
+        dev = grad.device
+        with _on(dev):
             rc = _lib.load().b200_ctc_grad_rescale(
                 grad.data_ptr(), _lib.dtype_code(grad.dtype), T, B, V, grad.stride(0), grad.stride(1),
-                gw.data_ptr(), gw.numel(), ctx.hint, ilen.data_ptr(), _stream(grad.device))
+                gw.data_ptr(), gw.numel(), ctx.hint, ilen.data_ptr(), _stream(dev))
         _lib.check(rc, "b200_ctc_grad_rescale")
-        return grad, None, None, None, None, None, None, None, None
+        return grad, None, None, None, None, None, None, None, None, None
 
 
 def upload_valid_frames(x_host, x_dev, ilen):
@@ -190,7 +283,8 @@ def upload_valid_frames(x_host, x_dev, ilen):
     return nbytes
 
 
-def ctc_nll(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, grad_scale_hint=1.0, strict=False):
+def ctc_nll(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, grad_scale_hint=1.0, strict=False,
+            reduce_scale=None):
     """Per-utterance negative log-likelihood (B,) fp32 from pre-softmax logits (T,B,V).
 
     targets: 1-D label buffer; utterance b's labels start at tgt_offsets[b] and there are
@@ -199,9 +293,12 @@ def ctc_nll(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, grad_scale_
     grad_scale_hint: the upstream gradient d loss / d nll_b the caller expects (see the module
     docstring); any other upstream gradient is still honoured, at the price of one more pass over
     the gradient.  strict: raise ValueError for invalid targets (synchronises; without it such
-    utterances get a NaN loss and NaN gradient rows).
+    utterances get a NaN loss and NaN gradient rows).  tgt_offsets=None: targets are concatenated.
+    reduce_scale=s: return the 0-dim loss s * sum_b nll_b instead (grad_scale_hint is then the upstream
+    gradient expected for THAT loss).
     """
-    return _CTCLossFunction.apply(logits, targets, tgt_offsets, ilen, olen, lmax, blank, grad_scale_hint, strict)
+    return _CTCLossFunction.apply(logits, targets, tgt_offsets, ilen, olen, lmax, blank, grad_scale_hint, strict,
+                                  reduce_scale)
 
 
 def ctc_loss_fwd_bwd(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, grad_weight=None,
@@ -227,7 +324,7 @@ def ctc_loss_fwd_bwd(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, gr
     with torch.cuda.device(dev):
         rc = _lib.load().b200_ctc_loss_fwd_bwd(
             *plan.common_args(), None if gw is None else gw.data_ptr(), float(grad_scale),
-            nll.data_ptr(), loss_sum.data_ptr(), grad.data_ptr(), grad.stride(0), grad.stride(1),
+            nll.data_ptr(), loss_sum.data_ptr(), 1.0, grad.data_ptr(), grad.stride(0), grad.stride(1),
             plan.ws_ptr, plan.ws_bytes, _stream(dev))
     _lib.check(rc, "b200_ctc_loss_fwd_bwd")
     return nll, loss_sum, grad
@@ -246,7 +343,7 @@ def ctc_loss_split(logits, targets, tgt_offsets, ilen, olen, lmax, blank=0, grad
     gw = None if grad_weight is None else grad_weight.to(device=dev, dtype=torch.float32).contiguous()
     lib = _lib.load()
     with torch.cuda.device(dev):
-        rc = lib.b200_ctc_loss_forward(*plan.common_args(), nll.data_ptr(), None, plan.ws_ptr, plan.ws_bytes,
+        rc = lib.b200_ctc_loss_forward(*plan.common_args(), nll.data_ptr(), None, 1.0, plan.ws_ptr, plan.ws_bytes,
                                        _stream(dev))
         _lib.check(rc, "b200_ctc_loss_forward")
         rc = lib.b200_ctc_loss_backward(*plan.common_args(), None if gw is None else gw.data_ptr(), float(grad_scale),

@@ -61,6 +61,8 @@ class CTCPrefixScorer(_ScorerBase):
     # ---- shared helpers
     def _build(self, x):
         logp = self.ctc.log_softmax(x.unsqueeze(0)).detach()  # assuming batch_size = 1
+        if not logp.is_cuda and torch.cuda.is_available():
+            logp = logp.cuda()   # encoder output left on the host by the caller: the scorer itself is CUDA only
         xlen = torch.tensor([logp.size(1)])
         self.impl = CTCPrefixScoreB200(logp, xlen, 0, self.eos)
 
@@ -95,7 +97,12 @@ class CTCPrefixScorer(_ScorerBase):
             (scores (n_hyps, n_vocab), batch state for select_state)
         """
         batch_state = self._resolve(state)
-        return self.impl(y, batch_state, ids)
+        scores, new_state = self.impl(y, batch_state, ids)
+        if x is not None and scores.device != x.device:
+            # a host-side search (the reference's BatchBeamSearch keeps its hypotheses in CPU tensors) around
+            # the CUDA scorer: only the (n_hyps, n_vocab) score matrix crosses, the states stay on the device
+            scores = scores.to(x.device)
+        return scores, new_state
 
     def batch_select_state(self, state, prev_hyp_ids, new_token_ids):
         """All survivors of a step at once, ids as device tensors (no host round trip): what

@@ -85,6 +85,9 @@ const char* b200_last_error(void);
  * Lmax        host-side upper bound on olen (sizes the lattice workspace).
  * nll         fp32 (B,) out: -log p(y_b | x_b) in nats; +inf if no alignment
  *             exists (torch.nn.CTCLoss, zero_infinity=False).
+ * loss_sum    fp32 (1,) out, may be NULL: loss_scale * sum_b nll[b], summed in a fixed order by the
+ *             lattice kernel that finishes last (CTC.loss_fn's "/ B" is loss_scale = 1/B: the
+ *             reduced loss needs no further kernel).
  * workspace   b200_ctc_loss_workspace_bytes(...) bytes, 256-byte aligned; it
  *             carries the lattice from _forward to _backward and must stay
  *             untouched in between.
@@ -97,7 +100,8 @@ int b200_ctc_loss_forward(const void* logits, int dtype,
                           const int64_t* targets, const int64_t* tgt_offsets,
                           const int64_t* ilen, const int64_t* olen,
                           int64_t Lmax, int blank,
-                          float* nll, float* loss_sum /* may be NULL: sum_b nll[b] */,
+                          float* nll,
+                          float* loss_sum /* may be NULL: loss_scale * sum_b nll[b] */, float loss_scale,
                           void* workspace, size_t workspace_bytes, void* stream);
 
 /* grad_logits[t,b,v] = grad_scale * grad_weight[b] *
@@ -130,7 +134,7 @@ int b200_ctc_loss_fwd_bwd(const void* logits, int dtype,
                           const int64_t* ilen, const int64_t* olen,
                           int64_t Lmax, int blank,
                           const float* grad_weight, float grad_scale,
-                          float* nll, float* loss_sum,
+                          float* nll, float* loss_sum, float loss_scale,
                           void* grad_logits, int64_t gstride_t, int64_t gstride_b,
                           void* workspace, size_t workspace_bytes, void* stream);
 

@@ -51,7 +51,7 @@ def walk_vs_reference_th(c, nsteps, make_ours, snum=0, margin=0, seed=0, follow=
         best = hyp * V + tok
         so, r1, sv1 = ours.select(st1, best)
         sr = ref.index_select_state(st2, best.to(device))
-        close(r1, sr[0].cpu().numpy(), step)
-        close(sv1, sr[1][:, 0].cpu().numpy(), step)
+        close(r1, sr[0].cpu().numpy(), step, "r")
+        close(sv1, sr[1][:, 0].cpu().numpy(), step, "s")
         parent = (hyp + torch.arange(B).view(-1, 1) * H).view(-1)
         y = [y[int(parent[k])] + [int(tok.view(-1)[k])] for k in range(B * H)]

@@ -45,7 +45,7 @@ def test_invalid_arguments_are_reported(lib):
 
     def fwd(dtype=0, blank=0, ws=p, ws_bytes=1 << 15, Lmax=2, V=8):
         return lib.b200_ctc_loss_forward(p, dtype, args["T"], args["B"], V, args["st"], args["sb"], p, p, p, p,
-                                         Lmax, blank, p, None, ws, ws_bytes, None)
+                                         Lmax, blank, p, None, 1.0, ws, ws_bytes, None)
 
     assert fwd(dtype=7) == 1 and b"dtype" in lib.b200_last_error()
     assert fwd(blank=9) == 1 and b"blank" in lib.b200_last_error()

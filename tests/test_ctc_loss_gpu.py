@@ -198,7 +198,7 @@ def test_module_call_runs_the_one_pass_kernels(monkeypatch):
     loss = ctc(hs, torch.tensor([20, 15, 18]), torch.randint(1, 16, (3, 4), device="cuda"), torch.tensor([4, 2, 3]))
     loss.backward()
     torch.cuda.synchronize()
-    assert spy.calls == ["b200_ctc_loss_workspace_bytes", "b200_ctc_loss_fwd_bwd", "b200_ctc_grad_rescale"]
+    assert [c for c in spy.calls if c != "b200_ctc_loss_workspace_bytes"] == ["b200_ctc_loss_fwd_bwd", "b200_ctc_grad_rescale"]
     spy.calls.clear()
     with torch.no_grad():      # evaluation: no gradient is produced
         ctc(hs, torch.tensor([20, 15, 18]), torch.randint(1, 16, (3, 4), device="cuda"), torch.tensor([4, 2, 3]))

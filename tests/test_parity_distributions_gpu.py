@@ -81,7 +81,10 @@ def _check_loss(c, tag, dtype=None, split=False, tol=TOL_F32):
     _report(test=tag, dtype=str(dtype), split=split, nll_rel=e_nll, grad_rel=e_g, torch_f32_grad_rel=e_ref,
             torch_f32_nll_rel=float(np.abs(fn - rn).max() / np.abs(rn).max()), mean_nll=float(rn.mean()))
     assert np.isfinite(nll).all() and np.isfinite(grad).all()
-    np.testing.assert_allclose(nll, rn, rtol=TOL_F32, atol=1e-6)
+    # loss: 1e-5 relative; a converged model's nll (~1e-6 nats in all) is below what ANY float32 evaluation of
+    # T log-probabilities near zero resolves, the reference's included: there the bar is the reference's own error
+    T = c["x"].shape[1]
+    assert (np.abs(nll - rn) <= np.maximum(TOL_F32 * np.abs(rn), np.maximum(2 * np.abs(fn - rn), 1.2e-7 * T))).all()
     assert e_g <= max(tol, e_ref), (e_g, e_ref)
     return e_g, e_ref
 
@@ -114,7 +117,7 @@ def test_loss_padded_frames_next_to_real_ones():
     nll, grad = _ours(c)
     c2 = dict(c, x=torch.nan_to_num(c["x"], nan=0.0))
     rn, rg = _torch_ref(c2, torch.float64)
-    np.testing.assert_allclose(nll, rn, rtol=TOL_F32, atol=1e-6)
+    np.testing.assert_allclose(nll, rn, rtol=TOL_F32, atol=1.2e-7 * 200)
     assert _normrel(grad, rg, 1.0 / 8) <= TOL_F32
     for b in range(8):
         assert (grad[b, int(c["ilen"][b]):] == 0).all()
@@ -141,14 +144,17 @@ def test_loss_c5_full_batch():
 ATOL = 1e-4
 
 
-def _close(got, ref, atol=ATOL, tag=None):
+def _close(got, ref, atol=ATOL, tag=None, ulps=2):
+    """atol absolute, plus `ulps` float32 spacings of the value itself: forward variables and eos scores reach
+    magnitudes of several thousand, where one float32 spacing is 5e-4 and two float32 evaluations in different
+    operation order (the reference's included) differ by a few of them."""
     got, ref = np.asarray(got, dtype=np.float64), np.asarray(ref, dtype=np.float64)
     real = np.abs(ref) < 1e9
     assert (got[~real] < -1e9).all(), "an entry the reference sets to its log(0) sentinel is finite here"
     assert (got[real] > -1e9).all(), "an entry the reference computes is the log(0) sentinel here"
     if real.any():
         err = np.abs(got[real] - ref[real])
-        tol = atol + 2.4e-7 * np.abs(ref[real])   # one fp32 spacing of the value itself
+        tol = atol + ulps * 1.2e-7 * np.abs(ref[real])
         if tag:
             _report(test=tag, max_abs_err=float(err.max()), max_abs_ref=float(np.abs(ref[real]).max()))
         assert (err <= tol).all(), float((err - tol).max())
@@ -171,7 +177,8 @@ def _walk_vs_reference_th(c, nsteps, snum=0, margin=0, seed=0, tag=None, follow=
             return so, so[0].cpu().numpy(), so[1].cpu().numpy()
 
     walk_vs_reference_th(c, nsteps, Ours, snum=snum, margin=margin, seed=seed, follow=follow, device="cuda",
-                         close=lambda got, ref, step: _close(got, ref, tag=tag and f"{tag}_step{step}"))
+                         close=lambda got, ref, step, what="scores": _close(
+                             got, ref, tag=tag and what == "scores" and f"{tag}_step{step}", ulps=2 if what == "scores" else 6))
 
 
 @pytest.mark.parametrize("kind", ["scale8", "scale30", "trained", "mismatch", "level"])
