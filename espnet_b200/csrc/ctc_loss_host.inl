@@ -283,6 +283,28 @@ extern "C" int b200_ctc_loss_stream_pass(const void* logits, int dtype, int64_t 
   return B200_OK;
 }
 
+extern "C" int b200_ctc_stage_labels(const int64_t* targets_host, int64_t n_targets, const int64_t* tgt_offsets_host,
+                                     const int64_t* ilen_host, const int64_t* olen_host, int64_t B,
+                                     int64_t* pinned_host, int64_t* dev, void* stream) {
+  B200_CHECK_ARG((targets_host || n_targets == 0) && ilen_host && olen_host && pinned_host && dev,
+                 B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(n_targets >= 0 && B >= 1, B200_ERR_INVALID_ARGUMENT, "bad sizes");
+  int64_t* q = pinned_host;
+  if (n_targets) memcpy(q, targets_host, sizeof(int64_t) * (size_t)n_targets);
+  q += n_targets;
+  if (tgt_offsets_host) {
+    memcpy(q, tgt_offsets_host, sizeof(int64_t) * (size_t)B);
+  } else {  // concatenated targets: exclusive prefix sum of the lengths
+    int64_t run = 0;
+    for (int64_t b = 0; b < B; ++b) { q[b] = run; run += olen_host[b] > 0 ? olen_host[b] : 0; }
+  }
+  memcpy(q + B, ilen_host, sizeof(int64_t) * (size_t)B);
+  memcpy(q + 2 * B, olen_host, sizeof(int64_t) * (size_t)B);
+  B200_CUDA(cudaMemcpyAsync(dev, pinned_host, sizeof(int64_t) * (size_t)(n_targets + 3 * B), cudaMemcpyHostToDevice,
+                            (cudaStream_t)stream));
+  return B200_OK;
+}
+
 extern "C" int b200_ctc_loss_status(const void* workspace, int64_t T, int64_t B, int64_t V, int64_t Lmax,
                                     int32_t* n_invalid_host, void* stream) {
   B200_CHECK_ARG(workspace && n_invalid_host, B200_ERR_INVALID_ARGUMENT, "null pointer argument");

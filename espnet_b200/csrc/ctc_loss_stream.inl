@@ -103,11 +103,13 @@ __device__ __forceinline__ StreamRow stream_row(const LossParams& p, int64_t bas
 template <typename T> struct StreamMid;
 template <> struct StreamMid<float> {
   static constexpr float kBias = 0.f;
+  static constexpr float kUnbias = 1.f;
   __device__ static __forceinline__ uint4 pack(const float* e) { return pack16<float>(e); }
   __device__ static __forceinline__ void unpack(const uint4& q, float* e) { unpack16<float>(q, e); }
 };
 template <> struct StreamMid<__nv_bfloat16> {
   static constexpr float kBias = 14.f;
+  static constexpr float kUnbias = 1.f / 16384.f;
   __device__ static __forceinline__ uint4 pack(const float* e) { return pack16<__half>(e); }
   __device__ static __forceinline__ void unpack(const uint4& q, float* e) { unpack16<__half>(q, e); }
 };
@@ -260,7 +262,8 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
       } else {
         __syncwarp();
       }
-      const float ml = mx * B200_LOG2E - StreamMid<T>::kBias;
+      const float mlog = mx * B200_LOG2E;
+      const float ml = mlog - StreamMid<T>::kBias;
       // pass 2: exponentials, summed in fp32 and kept in place
       float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
       drive([&](int j0, auto n_) {
@@ -293,7 +296,10 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
       } else {
         __syncwarp();
       }
-      const float l2 = ml + lg2f(ssum);  // row log2-sum-exp (the bias cancels)
+      // row log2-sum-exp.  The bias is taken out of the sum (an exact power of two) BEFORE the logarithm: adding
+      // -14 and +14.0000x in fp32 would quantise the result to 1e-6, which a converged model's per-frame
+      // log-probability (~ -1e-6) does not survive over 500 frames
+      const float l2 = mlog + lg2f(ssum * StreamMid<T>::kUnbias);
       // blank and label columns -> lpg (log2-probabilities)
 #pragma unroll
       for (int g = 0; g < kStreamGather; ++g) {

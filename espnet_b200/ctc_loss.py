@@ -52,10 +52,11 @@ class _PinnedRing(object):
     """A few pinned host buffers per device for the label side of a call, reused round-robin.  A slot is reused
     only after the copy that last read it has completed (one CUDA event per slot, normally long done)."""
 
-    SLOTS = 8
+    SLOTS = 16
 
     def __init__(self):
-        self.buf, self.np, self.ev, self.i = [None] * self.SLOTS, [None] * self.SLOTS, [None] * self.SLOTS, 0
+        n = self.SLOTS
+        self.buf, self.np, self.ptr, self.ev, self.i = [None] * n, [None] * n, [0] * n, [None] * n, 0
 
     def take(self, n):
         k = self.i
@@ -65,15 +66,32 @@ class _PinnedRing(object):
         if self.buf[k] is None or self.buf[k].numel() < n:
             self.buf[k] = torch.empty(max(n, 16384), dtype=torch.int64, pin_memory=True)
             self.np[k] = self.buf[k].numpy()
+            self.ptr[k] = self.buf[k].data_ptr()
         return k
 
-    def sent(self, k):
+    def sent(self, k, stream):
         if self.ev[k] is None:
             self.ev[k] = torch.cuda.Event()
-        self.ev[k].record()
+        self.ev[k].record(stream)
 
 
 _rings = {}
+
+
+def _ring(device):
+    r = _rings.get(device)
+    if r is None:
+        r = _rings[device] = _PinnedRing()
+    return r
+
+
+def _h64(x):
+    """A host-side label / length vector as a contiguous int64 CPU tensor (no copy when it already is one)."""
+    if not torch.is_tensor(x):
+        x = torch.as_tensor(x)
+    if x.dtype != torch.int64:
+        x = x.to(torch.int64)
+    return x if x.is_contiguous() else x.contiguous()
 
 
 def _host_np(x):
@@ -109,9 +127,7 @@ def pack_labels(targets, tgt_offsets, ilen, olen, device):
     if host:
         arrs = [_host_np(parts[k]) for k in host]
         n = sum(a.size for a in arrs)
-        ring = _rings.get(device)
-        if ring is None:
-            ring = _rings[device] = _PinnedRing()
+        ring = _ring(device)
         slot = ring.take(n)
         stage = ring.np[slot]
         o = 0
@@ -120,7 +136,7 @@ def pack_labels(targets, tgt_offsets, ilen, olen, device):
             o += a.size
         dev = torch.empty(n, dtype=torch.int64, device=device)
         dev.copy_(ring.buf[slot][:n], non_blocking=True)
-        ring.sent(slot)
+        ring.sent(slot, torch.cuda.current_stream(device))
         o = 0
         for k, a in zip(host, arrs):
             out[k] = dev[o:o + a.size]
@@ -135,32 +151,57 @@ _ws_bytes_cache = {}
 
 
 class _Plan(object):
-    """Device-side arguments shared by the kernels of one call."""
+    """Device-side arguments shared by the kernels of one call (raw pointers; `keep` owns the memory)."""
 
     def __init__(self, logits, targets, tgt_offsets, ilen, olen, lmax, blank):
         dev = logits.device
         self.logits = logits
-        self.T, self.B, self.V = logits.shape
-        self.targets, self.tgt_offsets, self.ilen, self.olen = pack_labels(targets, tgt_offsets, ilen, olen, dev)
-        if self.ilen.numel() != self.B or self.olen.numel() != self.B or self.tgt_offsets.numel() != self.B:
-            raise RuntimeError("ilen, olen and tgt_offsets must have one entry per utterance")
+        self.T, self.B, self.V = T, B, V = logits.shape
         self.lmax = int(lmax)
         self.blank = int(blank)
         self.dtype = _lib.dtype_code(logits.dtype)
-        key = (self.T, self.B, self.V, self.lmax)
+        self.stream = torch._C._cuda_getCurrentRawStream(dev.index) if dev.type == "cuda" else 0
+        lib = _lib.load()
+        host = [not (torch.is_tensor(p) and p.is_cuda) for p in (targets, ilen, olen)]
+        if all(host) and not (torch.is_tensor(tgt_offsets) and tgt_offsets.is_cuda) and dev.type == "cuda":
+            # the usual trainer-side call: labels and lengths arrive from the data loader on the host.  ONE pinned
+            # staging buffer, ONE asynchronous copy (laid out by the library), four pointers into the device copy
+            tg, il, ol = _h64(targets).reshape(-1), _h64(ilen).reshape(-1), _h64(olen).reshape(-1)
+            off = None if tgt_offsets is None else _h64(tgt_offsets).reshape(-1)
+            if il.numel() != B or ol.numel() != B or (off is not None and off.numel() != B):
+                raise RuntimeError("ilen, olen and tgt_offsets must have one entry per utterance")
+            nt = tg.numel()
+            n = nt + 3 * B
+            ring = _ring(dev)
+            slot = ring.take(n)
+            buf = torch.empty(n, dtype=torch.int64, device=dev)
+            base = buf.data_ptr()
+            with _on(dev):
+                rc = lib.b200_ctc_stage_labels(tg.data_ptr(), nt, None if off is None else off.data_ptr(), il.data_ptr(),
+                                               ol.data_ptr(), B, ring.ptr[slot], base, self.stream)
+            _lib.check(rc, "b200_ctc_stage_labels")
+            ring.sent(slot, torch.cuda.current_stream(dev))
+            self.keep = buf
+            self.targets_ptr, self.offsets_ptr = base, base + 8 * nt
+            self.ilen_ptr, self.olen_ptr = base + 8 * (nt + B), base + 8 * (nt + 2 * B)
+        else:
+            t = pack_labels(targets, tgt_offsets, ilen, olen, dev)
+            if t[2].numel() != B or t[3].numel() != B or t[1].numel() != B:
+                raise RuntimeError("ilen, olen and tgt_offsets must have one entry per utterance")
+            self.keep = t
+            self.targets_ptr, self.offsets_ptr, self.ilen_ptr, self.olen_ptr = (x.data_ptr() for x in t)
+        key = (T, B, V, self.lmax)
         nbytes = _ws_bytes_cache.get(key)
         if nbytes is None:
-            nbytes = _ws_bytes_cache[key] = _lib.load().b200_ctc_loss_workspace_bytes(*key)
+            nbytes = _ws_bytes_cache[key] = lib.b200_ctc_loss_workspace_bytes(*key)
         self.workspace = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
-        base = self.workspace.data_ptr()
-        self.ws_ptr = (base + 255) // 256 * 256
+        self.ws_ptr = (self.workspace.data_ptr() + 255) // 256 * 256
         self.ws_bytes = nbytes
 
     def common_args(self):
         x = self.logits
         return (x.data_ptr(), self.dtype, self.T, self.B, self.V, x.stride(0), x.stride(1),
-                self.targets.data_ptr(), self.tgt_offsets.data_ptr(), self.ilen.data_ptr(),
-                self.olen.data_ptr(), self.lmax, self.blank)
+                self.targets_ptr, self.offsets_ptr, self.ilen_ptr, self.olen_ptr, self.lmax, self.blank)
 
     def invalid_utterances(self):
         """Number of utterances of the last call on this plan whose targets were invalid (a label outside
@@ -170,13 +211,13 @@ class _Plan(object):
         n = ctypes.c_int32(0)
         with torch.cuda.device(self.logits.device):
             rc = _lib.load().b200_ctc_loss_status(self.ws_ptr, self.T, self.B, self.V, self.lmax, ctypes.byref(n),
-                                                  _stream(self.logits.device))
+                                                  self.stream)
         _lib.check(rc, "b200_ctc_loss_status")
         return int(n.value)
 
 
 def _stream(device):
-    return torch.cuda.current_stream(device).cuda_stream
+    return torch._C._cuda_getCurrentRawStream(device.index)
 
 
 class _on(object):
@@ -215,7 +256,7 @@ class _CTCLossFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, logits, targets, tgt_offsets, ilen, olen, lmax, blank, hint, strict, reduce_scale):
-        logits = _prep_logits(logits.detach())
+        logits = _prep_logits(logits)
         plan = _Plan(logits, targets, tgt_offsets, ilen, olen, lmax, blank)
         dev = logits.device
         nll = torch.empty(plan.B, dtype=torch.float32, device=dev)
@@ -229,13 +270,15 @@ class _CTCLossFunction(torch.autograd.Function):
             with _on(dev):
                 rc = lib.b200_ctc_loss_fwd_bwd(
                     *plan.common_args(), None, ctx.hint * s, nll.data_ptr(), loss_ptr, s, grad.data_ptr(),
-                    grad.stride(0), grad.stride(1), plan.ws_ptr, plan.ws_bytes, _stream(dev))
-            _lib.check(rc, "b200_ctc_loss_fwd_bwd")
-            ctx.save_for_backward(grad, plan.ilen)
+                    grad.stride(0), grad.stride(1), plan.ws_ptr, plan.ws_bytes, plan.stream)
+            if rc:
+                _lib.check(rc, "b200_ctc_loss_fwd_bwd")
+            ctx.save_for_backward(grad)
+            ctx.labels, ctx.ilen_ptr = plan.keep, plan.ilen_ptr
         else:
             with _on(dev):
                 rc = lib.b200_ctc_loss_forward(
-                    *plan.common_args(), nll.data_ptr(), loss_ptr, s, plan.ws_ptr, plan.ws_bytes, _stream(dev))
+                    *plan.common_args(), nll.data_ptr(), loss_ptr, s, plan.ws_ptr, plan.ws_bytes, plan.stream)
             _lib.check(rc, "b200_ctc_loss_forward")
         if strict:
             _check_strict(plan)
@@ -244,7 +287,7 @@ class _CTCLossFunction(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, gout):
-        grad, ilen = ctx.saved_tensors
+        grad, = ctx.saved_tensors
         T, B, V = grad.shape
         gw = gout
         if gw.dtype != torch.float32:
@@ -258,8 +301,9 @@ class _CTCLossFunction(torch.autograd.Function):
         with _on(dev):
             rc = _lib.load().b200_ctc_grad_rescale(
                 grad.data_ptr(), _lib.dtype_code(grad.dtype), T, B, V, grad.stride(0), grad.stride(1),
-                gw.data_ptr(), gw.numel(), ctx.hint, ilen.data_ptr(), _stream(dev))
-        _lib.check(rc, "b200_ctc_grad_rescale")
+                gw.data_ptr(), gw.numel(), ctx.hint, ctx.ilen_ptr, _stream(dev))
+        if rc:
+            _lib.check(rc, "b200_ctc_grad_rescale")
         return grad, None, None, None, None, None, None, None, None, None
 
 

@@ -153,6 +153,17 @@ int b200_ctc_loss_stream_pass(const void* logits, int dtype,
                               void* grad_logits, int64_t gstride_t, int64_t gstride_b,
                               void* workspace, size_t workspace_bytes, void* stream);
 
+/* Host-side helper for the label arguments of the calls above: lays [targets | tgt_offsets | ilen | olen]
+ * out in the caller's PINNED host buffer (n_targets + 3B int64) and starts ONE asynchronous copy to `dev`
+ * (same size) on `stream`.  tgt_offsets_host == NULL means "targets are concatenated" (what CTC.loss_fn
+ * receives, espnet2/asr/ctc.py:85): the offsets are the exclusive prefix sum of olen.  The four device
+ * arrays are then dev, dev + n_targets, dev + n_targets + B, dev + n_targets + 2B.  The pinned buffer may be
+ * reused once the copy has completed (the caller orders that with an event). */
+int b200_ctc_stage_labels(const int64_t* targets_host, int64_t n_targets,
+                          const int64_t* tgt_offsets_host,
+                          const int64_t* ilen_host, const int64_t* olen_host, int64_t B,
+                          int64_t* pinned_host, int64_t* dev, void* stream);
+
 /* Number of utterances of the last _forward / _fwd_bwd call on `workspace` whose targets were
  * invalid: a label outside [0,V), a label equal to blank, or olen[b] > Lmax.  torch.nn.CTCLoss
  * raises for such input on the CPU (espnet2/asr/ctc.py:49 calls it); here the kernels clamp the
