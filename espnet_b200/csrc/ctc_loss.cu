@@ -22,7 +22,7 @@ __global__ void ctc_prep_kernel(LossParams p) {
   // completes before any of them runs, so no separate memset node is needed in front of a call
   if (blockIdx.x == 0 && threadIdx.x < 8) p.ws.bad[threadIdx.x] = 0;
   __shared__ int s_bad;
-  if (threadIdx.x == 0) { p.ws.done[b] = 0; s_bad = (Lraw != L) ? 1 : 0; }
+  if (threadIdx.x == 0) { p.ws.done[b] = 0; p.ws.redo[b] = 0; s_bad = (Lraw != L) ? 1 : 0; }
   __syncthreads();
   for (int64_t i = threadIdx.x; i < L; i += blockDim.x) {
     int64_t v = y[i];
@@ -83,6 +83,7 @@ __global__ void ctc_loss_sum_kernel(const float* nll, int B, float* out) {
 }  // namespace b200
 
 #include "ctc_loss_sweep.inl"
+#include "ctc_loss_lin.inl"
 #include "ctc_loss_rows.inl"
 #include "ctc_loss_occ.inl"
 #include "ctc_loss_stream.inl"

@@ -48,6 +48,16 @@ struct LossWs {
                     //             its gradient rows are NaN (a corrupt target batch must not train silently)
   int* order;       // [B]         utterances by decreasing ilen (rank -> b): long lattices start first
   int* done;        // [B]         finished sweeps of utterance b (2 = its alpha and beta lattices are complete)
+  // ---- linear-domain (fp64) sweeps, ctc_loss_lin.inl
+  double* pd;       // [B][T][Kp]  2^(lpg + gff): the probabilities of blank / labels as doubles, scaled per frame
+                    //             so that the largest of them is in [1, 2) (feed-forward scale)
+  int* gff;         // [B][T]      that per-frame scale exponent (>= 0)
+  int* gcum;        // [2][B][T]   cumulative feed-forward exponent along each sweep direction, up to and incl. frame t
+  int* gwarp;       // [2][B][ceil(T/8)][8]  block (warp) scale exponent of the sweep during chunk c:
+                    //             true value = stored * 2^-(gcum + gwarp)
+  int* gtot;        // [B]         sum over the frames of gff
+  int* redo;        // [B]         1: the linear sweep could not certify utterance b (range), the log-domain
+                    //             kernels redo it
   int64_t Kp, Sp;
   size_t bytes;
 };
@@ -58,7 +68,8 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 inline LossWs carve_loss_ws(void* base, int64_t T, int64_t B, int64_t V, int64_t Lmax) {
   (void)V;
   LossWs w;
-  w.Kp = (int64_t)align_up((size_t)(Lmax + 1), 8);
+  // (one spare slot after the L+1 columns: the stream kernel leaves the frame's feed-forward exponent there)
+  w.Kp = (int64_t)align_up((size_t)(Lmax + 2), 8);
   w.Sp = 2 * w.Kp;
   size_t off = 0;
   char* p = (char*)base;
@@ -77,6 +88,12 @@ inline LossWs carve_loss_ws(void* base, int64_t T, int64_t B, int64_t V, int64_t
   w.badutt = (int*)take(sizeof(int) * B);
   w.order = (int*)take(sizeof(int) * B);
   w.done = (int*)take(sizeof(int) * B);
+  w.pd = (double*)take(sizeof(double) * B * T * w.Kp);
+  w.gff = (int*)take(sizeof(int) * B * T);
+  w.gcum = (int*)take(sizeof(int) * 2 * B * T);
+  w.gwarp = (int*)take(sizeof(int) * 2 * B * ((T + 7) / 8) * 8);
+  w.gtot = (int*)take(sizeof(int) * B);
+  w.redo = (int*)take(sizeof(int) * B);
   w.bytes = off;
   return w;
 }
@@ -101,6 +118,8 @@ struct LossParams {
   float* loss_sum; // loss_scale * sum_b nll[b], written by the sweep CTA that finishes last (may be NULL)
   float loss_scale;
   int prep_after_stream;  // fused call: the prep kernel is a programmatic dependent of the stream kernel
+  int lin;        // the stream kernel also writes pd / gff for the linear-domain sweeps
+  int redo_mode;  // log-domain sweep / patch kernels: only the utterances flagged in ws.redo
 };
 
 // label count of utterance b as every kernel uses it: olen clamped to the Lmax the workspace was sized for

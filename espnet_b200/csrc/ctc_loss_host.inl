@@ -118,6 +118,8 @@ static LossParams make_params(const void* logits, int64_t T, int64_t B, int64_t 
 }
 
 static int launch_prep(const LossParams& p, cudaStream_t st);
+// test hook (b200_ctc_debug_force_log_sweep): run the fused call on the log-domain sweeps only
+static int g_force_log_sweep = 0;
 
 static int run_forward(LossParams p, int dtype, float* loss_sum, float loss_scale, cudaStream_t st) {
   const int es = elem_size(dtype);
@@ -163,11 +165,21 @@ static int run_fused(LossParams p, int dtype, float* loss_sum, float loss_scale,
   // as a programmatic dependent and runs under it.  stream -> prep -> sweeps -> patch are all chained by
   // programmatic dependent launch; every grid ends with griddepcontrol.wait so that completion is transitive.
   p.prep_after_stream = 1;
+  p.lin = (lin_sweep_ok(p) && !g_force_log_sweep) ? 1 : 0;
   int rc = launch_stream(p, dtype, sc, st);
   if (rc) return rc;
   if (stream_only) { *done = true; return B200_OK; }
   rc = launch_prep(p, st);
   if (rc) return rc;
+  if (p.lin) {
+    // linear-domain (float64) sweeps, then the patch kernel, which certifies every row it decodes; utterances it
+    // cannot certify are redone by the log-domain sweeps and a second patch pass (both exit at once otherwise)
+    rc = launch_sweep_lin(p, st, true);
+    if (rc) return rc;
+    rc = launch_patch(p, dtype, st, true);
+    if (rc) return rc;
+    p.redo_mode = 1;
+  }
   rc = launch_sweep(p, st, true);
   if (rc) return rc;
   rc = launch_patch(p, dtype, st);
@@ -283,6 +295,12 @@ extern "C" int b200_ctc_loss_stream_pass(const void* logits, int dtype, int64_t 
   return B200_OK;
 }
 
+extern "C" int b200_ctc_debug_force_log_sweep(int on) {
+  const int was = g_force_log_sweep;
+  g_force_log_sweep = on ? 1 : 0;
+  return was;
+}
+
 extern "C" int b200_ctc_stage_labels(const int64_t* targets_host, int64_t n_targets, const int64_t* tgt_offsets_host,
                                      const int64_t* ilen_host, const int64_t* olen_host, int64_t B,
                                      int64_t* pinned_host, int64_t* dev, void* stream) {
@@ -306,19 +324,22 @@ extern "C" int b200_ctc_stage_labels(const int64_t* targets_host, int64_t n_targ
 }
 
 extern "C" int b200_ctc_loss_status(const void* workspace, int64_t T, int64_t B, int64_t V, int64_t Lmax,
-                                    int32_t* n_invalid_host, void* stream) {
+                                    int32_t* n_invalid_host, int32_t* n_redone_host, void* stream) {
   B200_CHECK_ARG(workspace && n_invalid_host, B200_ERR_INVALID_ARGUMENT, "null pointer argument");
   B200_CHECK_ARG(T >= 1 && B >= 1 && V >= 1 && Lmax >= 0 && B < (1ll << 30), B200_ERR_INVALID_ARGUMENT, "bad sizes");
   const LossWs ws = carve_loss_ws(const_cast<void*>(workspace), T, B, V, Lmax);
-  int* host = (int*)malloc(sizeof(int) * (size_t)B);
+  int* host = (int*)malloc(sizeof(int) * 2 * (size_t)B);
   B200_CHECK_ARG(host != nullptr, B200_ERR_INVALID_ARGUMENT, "out of host memory");
   cudaError_t e = cudaMemcpyAsync(host, ws.badutt, sizeof(int) * (size_t)B, cudaMemcpyDeviceToHost, (cudaStream_t)stream);
-  if (e == cudaSuccess) e = cudaStreamSynchronize((cudaStream_t)stream);
-  int n = 0;
   if (e == cudaSuccess)
-    for (int64_t b = 0; b < B; ++b) n += host[b] ? 1 : 0;
+    e = cudaMemcpyAsync(host + B, ws.redo, sizeof(int) * (size_t)B, cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize((cudaStream_t)stream);
+  int n = 0, r = 0;
+  if (e == cudaSuccess)
+    for (int64_t b = 0; b < B; ++b) { n += host[b] ? 1 : 0; r += host[B + b] ? 1 : 0; }
   free(host);
   if (e != cudaSuccess) return cuda_fail(e, "b200_ctc_loss_status");
   *n_invalid_host = n;
+  if (n_redone_host) *n_redone_host = r;
   return B200_OK;
 }

@@ -29,7 +29,8 @@ constexpr int kOccMaxStages = 4;  // rows in flight per warp
 
 // floats of one stage (alpha row, beta row, lpg row) and of one warp's share of shared memory:
 // stages, un-normalised occupancies [2][Kp], label columns [Kp], 16-bit duplicate codes [Kp]
-__host__ __device__ inline int64_t occ_stage_floats(int64_t Kp) { return 5 * Kp; }
+// (+16: the block scale exponents of the alpha and of the beta sweep for the row's chunks, linear lattice only)
+__host__ __device__ inline int64_t occ_stage_floats(int64_t Kp) { return 5 * Kp + 16; }
 __host__ __device__ inline int64_t occ_warp_floats(int64_t Kp, int stages) {
   return stages * occ_stage_floats(Kp) + 3 * Kp + Kp / 2;
 }
@@ -41,7 +42,9 @@ constexpr int kDup16NextMask = 0x7fff;
 //         four stages TWO rows are reduced together (two independent dependency chains per warp: the
 //         kernel is bound by the latency of one row's ~500 dependent instructions, not by issue slots);
 // NJ = 0: any L, every pass re-reads shared memory, one row at a time.
-template <typename T, bool PATCH, int NJ>
+// LIN: the lattice holds the HIGH WORDS of float64 states of the linear-domain sweeps (ctc_loss_lin.inl):
+//      true value = word-as-double * 2^-(gcum(t) + gwarp(chunk, block)); otherwise fp32 log2 values.
+template <typename T, bool PATCH, int NJ, bool LIN>
 __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) {
   extern __shared__ __align__(128) unsigned char occ_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -73,9 +76,16 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
   // kernel and a sweep CTA do not fit on one SM together) work through the finished utterances meanwhile.
   const int nb = p.b1 - p.b0;
   auto phys = [&](int i) { return p.ws.order[p.b0 + nb - 1 - i]; };
-  auto frames_of = [&](int i) { return i < nb ? max(min((int)p.ilen[phys(i)], T_), 0) : 0; };
+  // (redo pass: only the utterances the linear sweeps could not certify; their log-domain sweeps signal 3 and 4)
+  auto frames_of = [&](int i) {
+    if (i >= nb) return 0;
+    const int ub = phys(i);
+    if (p.redo_mode && !p.ws.redo[ub]) return 0;
+    return max(min((int)p.ilen[ub], T_), 0);
+  };
+  const int done_target = p.redo_mode ? 4 : 2;
   auto wait_done = [&](int ub) {  // lane 0 only
-    while (ld_acquire_s32(p.ws.done + ub) < 2) __nanosleep(256);
+    while (ld_acquire_s32(p.ws.done + ub) < done_target) __nanosleep(256);
   };
   int tot = 0;
   for (int base = 0; base < nb; base += 32) tot += frames_of(base + lane);
@@ -122,12 +132,14 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
   int bi = pi, b = pb, t = pt, Tb = pTb, L = pL;  // consumer
   float wgt = 1.f;
   bool poison = false;
+  bool lin_skip = false;        // LIN: nothing to do for this utterance here
+  int lin_k0 = 0, lin_cert = -0x40000000;  // LIN: scale reference of the utterance; largest certificate term so far
   // next utterance with frames (there is one whenever this is called: the range has rows left)
   auto next_utt = [&](int& ui, int& ub, int& uTb, int& uL) {
     do {
       ++ui;
       ub = phys(ui);
-      uTb = max(min((int)p.ilen[ub], T_), 0);
+      uTb = (p.redo_mode && !p.ws.redo[ub]) ? 0 : max(min((int)p.ilen[ub], T_), 0);
     } while (uTb == 0);
     uL = utt_labels(p, ub);
   };
@@ -140,6 +152,14 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
     if (PATCH) {
       wgt = p.grad_scale * (p.grad_weight ? p.grad_weight[b] : 1.0f);
       poison = !isfinite(p.ws.nll_ws[b]) || isnan(wgt);
+      if (LIN && p.ws.redo[b]) poison = false;  // (the redo pass owns this utterance)
+    }
+    if (LIN) {
+      // log2 p(y|x) and the sum of the feed-forward exponents: sum_s alpha_t(s) beta_t(s) / p_t(s) = p(y|x) in every
+      // frame, so every occupancy term is known to lie below this level and the relevant ones just below it
+      lin_skip = p.ws.redo[b] != 0 || !isfinite(p.ws.nll_ws[b]);
+      lin_k0 = p.ws.gtot[b] + (int)floorf(-p.ws.nll_ws[b] * B200_LOG2E) + 2046;
+      lin_cert = -0x40000000;
     }
     const int* lab = p.ws.labels + (int64_t)b * Kp;
     const int* dup = p.ws.dupcode + (int64_t)b * Kp;
@@ -150,18 +170,32 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
     }
     __syncwarp();
   };
+  // LIN: the rows of utterance b decoded so far are certified only if no flushed state could have mattered; otherwise
+  // the utterance goes to the log-domain kernels (any warp may raise the flag; the redo pass rewrites all of its rows)
+  auto lin_flush = [&]() {
+    if (LIN) {
+      const int c = __reduce_max_sync(0xffffffffu, lin_cert);
+      if (lane == 0 && c > -48 && !lin_skip) p.ws.redo[b] = 1;
+      lin_cert = -0x40000000;
+    }
+  };
   // copies of the producer's current row into stage s, then the cursor moves on
   int issued = 0;
   auto issue = [&](int s) {
     if (lane == 0) {
       const uint32_t nA = (uint32_t)(((2 * pL + 1) * 4 + 15) & ~15);  // bytes of a lattice row that are used
-      const uint32_t nL = (uint32_t)(((pL + 1) * 4 + 15) & ~15);
+      const uint32_t nL = LIN ? (uint32_t)(Kp * 4) : (uint32_t)(((pL + 1) * 4 + 15) & ~15);  // (LIN: gff in the last slot)
       const int64_t row = (int64_t)pb * T_ + pt;
       float* st = wbase + s * stagef;
-      mbar_arrive_expect_tx(&bars[s], 2 * nA + nL);
+      mbar_arrive_expect_tx(&bars[s], 2 * nA + nL + (LIN ? 64u : 0u));
       bulk_g2s(st, p.ws.lat + row * Sp, nA, &bars[s]);
       bulk_g2s(st + Sp, p.ws.lat + ((int64_t)p.B * T_ + row) * Sp, nA, &bars[s]);
       bulk_g2s(st + 2 * Sp, p.ws.lpg + row * Kp, nL, &bars[s]);
+      if (LIN) {
+        const int64_t nch = (T_ + 7) / 8;
+        bulk_g2s(st + 5 * Kp, p.ws.gwarp + ((int64_t)pb * nch + pt / 8) * 8, 32, &bars[s]);
+        bulk_g2s(st + 5 * Kp + 8, p.ws.gwarp + (((int64_t)p.B + pb) * nch + (pTb - 1 - pt) / 8) * 8, 32, &bars[s]);
+      }
     }
     ++issued;
     if (++pt == pTb && issued < n) {
@@ -175,7 +209,39 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
 
   {
     // un-normalised log2 occupancy of the blank state k (k <= L) and of the label state k (k < L)
+    // LIN: log2 of (alpha word * beta word) relative to the utterance's reference level kt, from exponent fields and
+    // 20-bit mantissas; -3e38 when either state is zero.  cert: the certificate term of a state with a zero word
+    // (what a flushed state could have carried, relative to p(y|x)); structural zeros (states that frame t cannot
+    // reach from either end) are not flushes.
+    auto lin_dec = [&](int wa, int wb, int ga, int gb, int kt, float lp, bool reach_a, bool reach_b, int& cert) -> float {
+      const int ea = wa >> 20, eb = wb >> 20;
+      if (ea == 0 || eb == 0) {
+        if ((ea == 0 && reach_a) || (eb == 0 && reach_b)) {
+          const int c = (ea ? ea : -51) + (eb ? eb : -51) - ga - gb - kt + 1 - (int)floorf(lp);
+          cert = max(cert, c);
+        }
+        return -3.0e38f;
+      }
+      const float ma = __int_as_float(0x3f800000 | ((wa & 0xfffff) << 3));
+      const float mb = __int_as_float(0x3f800000 | ((wb & 0xfffff) << 3));
+      return (float)(ea + eb - ga - gb - kt) + lg2f(ma * mb);
+    };
+    int lin_t = 0, lin_Tb = 0;  // frame / length of the row being decoded (reachability)
     auto logocc = [&](const float* st, int k, float& ub, float& ul) {
+      if (LIN) {
+        const int* si = reinterpret_cast<const int*>(st);
+        const int kt = lin_k0 + (int)st[2 * Sp + Kp - 1];  // + gff(t)
+        const int2 a = *reinterpret_cast<const int2*>(si + 2 * k);
+        const int ga = si[5 * Kp + (k >> 5)];
+        const int fa = 2 * lin_t + 1, fb = 2 * (lin_Tb - 1 - lin_t) + 1;  // highest reachable state index from either end
+        ub = lin_dec(a.x, si[Sp + 2 * (L - k)], ga, si[5 * Kp + 8 + ((L - k) >> 5)], kt, st[2 * Sp], 2 * k <= fa,
+                     2 * (L - k) <= fb, lin_cert) - st[2 * Sp];
+        ul = -3.0e38f;
+        if (k < L)
+          ul = lin_dec(a.y, si[Sp + 2 * (L - k) - 1], ga, si[5 * Kp + 8 + ((L - 1 - k) >> 5)], kt, st[2 * Sp + 1 + k],
+                       2 * k + 1 <= fa, 2 * (L - 1 - k) + 1 <= fb, lin_cert) - st[2 * Sp + 1 + k];
+        return;
+      }
       const float2 a = *reinterpret_cast<const float2*>(st + 2 * k);
       ub = a.x + st[Sp + 2 * (L - k)] - st[2 * Sp];
       ul = -3.0e38f;
@@ -229,6 +295,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
         for (int j = 0; j < N; ++j) {
           const int k = lane + 32 * j;
           ub[x][j] = -3.0e38f; ul[x][j] = -3.0e38f;
+          lin_t = t + x;
           if (k <= L) logocc(st[x], k, ub[x][j], ul[x][j]);
           m[x] = fmaxf(m[x], fmaxf(ub[x][j], ul[x][j]));
         }
@@ -265,6 +332,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
     };
     auto process_loop = [&](int t, const float* st) {
       float m = -3.0e38f, w_all = 0.f, w_blank = 0.f;
+      lin_t = t;
       for (int k = lane; k <= L; k += 32) {
         float ub, ul;
         logocc(st, k, ub, ul);
@@ -304,10 +372,13 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
           T* dst = grad + (int64_t)b * p.gstride_b + (int64_t)(t + x) * p.gstride_t;
           for (int v = lane; v < (int)p.V; v += 32) dst[v] = nanv;
         }
+      } else if (LIN && lin_skip) {
       } else if constexpr (NJ > 0) {
+        lin_Tb = Tb;
         if (cnt == 2) process_regs(std::integral_constant<int, 2>{}, t, st);
         else process_regs(std::integral_constant<int, 1>{}, t, st);
       } else {
+        lin_Tb = Tb;
         process_loop(t, st[0]);
       }
       __syncwarp();  // every lane is done with the stages (and with scratch) before they are refilled
@@ -316,11 +387,13 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
       r += cnt;
       t += cnt;
       if (t == Tb && r < n) {
+        lin_flush();
         next_utt(bi, b, Tb, L);
         t = 0;
         enter();
       }
     }
+    lin_flush();
   }
   }  // next ticket
   // this grid must not be seen as finished before the sweeps it ran under
@@ -347,41 +420,49 @@ static OccPlan plan_occ(int64_t Kp) {
   return OccPlan{0, 0, 0};
 }
 
-template <typename T, bool PATCH, int NJ>
+template <typename T, bool PATCH, int NJ, bool LIN>
 static int launch_occ_nj(const LossParams& p, cudaStream_t st) {
   const OccPlan pl = plan_occ(p.ws.Kp);
   B200_CHECK_ARG(pl.warps > 0, B200_ERR_UNSUPPORTED_SHAPE, "Lmax=%lld: a lattice row does not fit in shared memory",
                  (long long)p.Lmax);
-  B200_CUDA(set_max_smem_cached((const void*)ctc_occ_kernel<T, PATCH, NJ>, (int)pl.smem));
+  B200_CUDA(set_max_smem_cached((const void*)ctc_occ_kernel<T, PATCH, NJ, LIN>, (int)pl.smem));
   const int64_t units = (int64_t)(p.b1 - p.b0) * p.T;  // rows, at least one per warp
   int per_sm = 1;
-  B200_CUDA(max_blocks_per_sm_cached((const void*)ctc_occ_kernel<T, PATCH, NJ>, pl.warps * 32, pl.smem, &per_sm));
+  B200_CUDA(max_blocks_per_sm_cached((const void*)ctc_occ_kernel<T, PATCH, NJ, LIN>, pl.warps * 32, pl.smem, &per_sm));
   if (per_sm < 1) per_sm = 1;
   int64_t g = (units + pl.warps - 1) / pl.warps;
   const int64_t cap = (int64_t)num_sms() * per_sm;  // persistent: every CTA resident
   if (g > cap) g = cap;
   if (g < 1) g = 1;
-  B200_CUDA(launch_kernel(ctc_occ_kernel<T, PATCH, NJ>, dim3((unsigned)g), dim3(pl.warps * 32), pl.smem, st, PATCH, p,
+  B200_CUDA(launch_kernel(ctc_occ_kernel<T, PATCH, NJ, LIN>, dim3((unsigned)g), dim3(pl.warps * 32), pl.smem, st, PATCH, p,
                           pl.stages));
   return B200_OK;
 }
 
-template <typename T, bool PATCH>
+template <typename T, bool PATCH, bool LIN>
 static int launch_occ_t(const LossParams& p, cudaStream_t st) {
-  if (p.Lmax + 1 <= 32 * 5) return launch_occ_nj<T, PATCH, 5>(p, st);
-  if (p.Lmax + 1 <= 32 * 10) return launch_occ_nj<T, PATCH, 10>(p, st);
-  return launch_occ_nj<T, PATCH, 0>(p, st);
+  if (p.Lmax + 1 <= 32 * 5) return launch_occ_nj<T, PATCH, 5, LIN>(p, st);
+  if (LIN || p.Lmax + 1 <= 32 * 10) return launch_occ_nj<T, PATCH, 10, LIN>(p, st);  // (LIN: Lmax <= 255)
+  return launch_occ_nj<T, PATCH, 0, LIN>(p, st);
 }
 
 // occupancies into ws.occ (separate forward / backward calls)
-static int launch_occ(const LossParams& p, cudaStream_t st) { return launch_occ_t<float, false>(p, st); }
+static int launch_occ(const LossParams& p, cudaStream_t st) { return launch_occ_t<float, false, false>(p, st); }
 
-// blank / label columns of the gradient patched in place (fused forward + backward)
-static int launch_patch(const LossParams& p, int dtype, cudaStream_t st) {
+// blank / label columns of the gradient patched in place (fused forward + backward); lin: the lattice of the
+// linear-domain sweeps
+static int launch_patch(const LossParams& p, int dtype, cudaStream_t st, bool lin = false) {
+  if (lin) {
+    switch (dtype) {
+      case B200_F32: return launch_occ_t<float, true, true>(p, st);
+      case B200_BF16: return launch_occ_t<__nv_bfloat16, true, true>(p, st);
+      case B200_F16: return launch_occ_t<__half, true, true>(p, st);
+    }
+  }
   switch (dtype) {
-    case B200_F32: return launch_occ_t<float, true>(p, st);
-    case B200_BF16: return launch_occ_t<__nv_bfloat16, true>(p, st);
-    case B200_F16: return launch_occ_t<__half, true>(p, st);
+    case B200_F32: return launch_occ_t<float, true, false>(p, st);
+    case B200_BF16: return launch_occ_t<__nv_bfloat16, true, false>(p, st);
+    case B200_F16: return launch_occ_t<__half, true, false>(p, st);
   }
   set_error("unknown dtype %d", dtype);
   return B200_ERR_INVALID_ARGUMENT;

@@ -115,6 +115,16 @@ template <> struct StreamMid<__nv_bfloat16> {
 };
 template <> struct StreamMid<__half> : StreamMid<__nv_bfloat16> {};
 
+// 2^x for x <= ~1 as a double: fraction through ex2.approx (fp32, 2^-22 relative), integer part through the exponent
+// field; below 2^-1021 the result is 0 (what the linear sweeps treat as "impossible")
+__device__ __forceinline__ double exp2_scaled(float x) {
+  const float e = floorf(x);
+  const float m = ex2f(x - e);  // [1, 2)
+  if (!(e > -1021.0f)) return 0.0;
+  const double d = (double)m;
+  return __hiloint2double(__double2hiint(d) + ((int)e << 20), __double2loint(d));
+}
+
 __device__ __forceinline__ void group_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
@@ -125,7 +135,7 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
   uint64_t* full = reinterpret_cast<uint64_t*>(st_smem);  // [kStreamMaxSlots]
   uint64_t* empty = full + kStreamMaxSlots;               // [kStreamMaxSlots]
   unsigned char* slots = st_smem + 2 * kStreamMaxSlots * sizeof(uint64_t);
-  __shared__ float s_mx[kStreamWarps], s_sm[kStreamWarps];
+  __shared__ float s_mx[kStreamWarps], s_sm[kStreamWarps], s_gx[kStreamWarps];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int PER = ElemTraits<T>::kPerVec;
   constexpr int GT = 32 * G;               // threads per row group
@@ -233,8 +243,16 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
       // nobody reads before the patch kernel; lpg itself only ever receives FINAL values, because the
       // sweeps running under this kernel treat any non-NaN word of lpg as valid)
       float* park = p.ws.occ + row * Kp;
-      for (int kk = gtid + GT * kStreamGather; kk <= L; kk += GT)
-        park[kk] = ElemTraits<T>::to_float(sT[label_at(kk - 1)]) * B200_LOG2E;
+      // largest raw value among the blank / label columns (for the feed-forward scale of the linear sweeps)
+      float gx = -3.0e38f;
+#pragma unroll
+      for (int g = 0; g < kStreamGather; ++g)
+        if (gtid + GT * g <= L) gx = fmaxf(gx, xg[g]);
+      for (int kk = gtid + GT * kStreamGather; kk <= L; kk += GT) {
+        const float v = ElemTraits<T>::to_float(sT[label_at(kk - 1)]);
+        gx = fmaxf(gx, v);
+        park[kk] = v * B200_LOG2E;
+      }
       // Every thread of the group owns the vectors gtid + GT*u; the first nfull of them exist for
       // every thread (no bounds checks in the unrolled loops), at most one more for some.
       auto drive = [&](auto pass) {
@@ -287,12 +305,13 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
         }
       });
       float ssum = warp_sum((s0 + s1) + (s2 + s3));
+      gx = warp_max(gx);
       if (G > 1) {
-        if (lane == 0) s_sm[warp] = ssum;
+        if (lane == 0) { s_sm[warp] = ssum; s_gx[warp] = gx; }
         group_sync(bar_id, GT);
         ssum = 0.f;
 #pragma unroll
-        for (int g = 0; g < G; ++g) ssum += s_sm[grp * G + g];
+        for (int g = 0; g < G; ++g) { ssum += s_sm[grp * G + g]; gx = fmaxf(gx, s_gx[grp * G + g]); }
       } else {
         __syncwarp();
       }
@@ -301,13 +320,28 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
       // log-probability (~ -1e-6) does not survive over 500 frames
       const float l2 = mlog + lg2f(ssum * StreamMid<T>::kUnbias);
       // blank and label columns -> lpg (log2-probabilities)
+      // feed-forward scale of the linear sweeps: the largest needed probability of the frame lands in [1, 2)
+      const float maxlp = fmaf(gx, B200_LOG2E, -l2);
+      const float gf = (p.lin && maxlp > -1.0e29f) ? -floorf(maxlp) : 0.f;
+      double* pdo = p.ws.pd + row * Kp;
 #pragma unroll
       for (int g = 0; g < kStreamGather; ++g) {
         const int kk = gtid + GT * g;
-        if (kk <= L) st_relaxed_f32(lpo + kk, fmaxf(fmaf(xg[g], B200_LOG2E, -l2), B200_NEG));
+        if (kk <= L) {
+          const float lp = fmaxf(fmaf(xg[g], B200_LOG2E, -l2), B200_NEG);
+          st_relaxed_f32(lpo + kk, lp);
+          if (p.lin) pdo[kk] = exp2_scaled(lp + gf);
+        }
       }
-      for (int kk = gtid + GT * kStreamGather; kk <= L; kk += GT)
-        st_relaxed_f32(lpo + kk, fmaxf(park[kk] - l2, B200_NEG));
+      for (int kk = gtid + GT * kStreamGather; kk <= L; kk += GT) {
+        const float lp = fmaxf(park[kk] - l2, B200_NEG);
+        st_relaxed_f32(lpo + kk, lp);
+        if (p.lin) pdo[kk] = exp2_scaled(lp + gf);
+      }
+      if (p.lin && gtid == 0) {
+        p.ws.gff[row] = (int)gf;
+        st_relaxed_f32(lpo + Kp - 1, gf);
+      }
       if (gtid == 0) p.ws.lse2[row] = l2;
       // pass 3: e * (w / sum) in the output type, in place
       const float scale = wgt / ssum;

@@ -51,19 +51,24 @@ __device__ __forceinline__ float clamp_int_f(float x) {  // integer-valued, safe
 
 // Final value of utterance b; the CTA that delivers the last one also sums them (fixed order:
 // the sum is deterministic).
-__device__ __forceinline__ void sweep_finish_nll(const LossParams& p, int b, float nll) {
-  if (p.ws.badutt[b]) nll = __int_as_float(0x7fc00000);  // invalid labels / olen > Lmax: loud, not silent
-  p.nll[b] = nll;
-  p.ws.nll_ws[b] = nll;
+// One call per utterance and pass (by its alpha CTA) once the utterance's nll is final for that pass; the caller that
+// delivers the last one sums them in a fixed order.  (The redo pass of the log-domain kernels counts separately.)
+__device__ __forceinline__ void sweep_count_nll(const LossParams& p) {
   if (p.loss_sum == nullptr) return;
   __threadfence();
-  const int done = atomicAdd(p.ws.bad + 4, 1);
+  const int done = atomicAdd(p.ws.bad + (p.redo_mode ? 6 : 4), 1);
   if (done == (p.b1 - p.b0) - 1) {
     __threadfence();
     float s = 0.f;
     for (int o = p.b0; o < p.b1; ++o) s += ld_cg_f32(p.nll + o);
     *p.loss_sum = s * p.loss_scale;
   }
+}
+__device__ __forceinline__ void sweep_finish_nll(const LossParams& p, int b, float nll) {
+  if (p.ws.badutt[b]) nll = __int_as_float(0x7fc00000);  // invalid labels / olen > Lmax: loud, not silent
+  p.nll[b] = nll;
+  p.ws.nll_ws[b] = nll;
+  sweep_count_nll(p);
 }
 
 template <int MAXT> struct SweepRings {
@@ -87,6 +92,10 @@ __global__ void __launch_bounds__(MAXT) ctc_sweep_kernel(LossParams p) {
   pdl_launch_dependents();
   const int b = p.ws.order[p.b0 + blockIdx.x];
   const int d = blockIdx.y;
+  if (p.redo_mode && !p.ws.redo[b]) {  // only what the linear sweeps could not certify
+    if (threadIdx.x == 0 && d == 0) sweep_count_nll(p);
+    return;
+  }
   const int Tb = min((int)p.ilen[b], (int)p.T);
   const int L = utt_labels(p, b);
   const int i = threadIdx.x;
@@ -396,6 +405,10 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
   pdl_launch_dependents();
   __syncthreads();
   const int b = p.ws.order[p.b0 + blockIdx.x];
+  if (p.redo_mode && !p.ws.redo[b]) {  // only what the linear sweeps could not certify
+    if (i == 0 && d == 0) sweep_count_nll(p);
+    return;
+  }
   const int Tb = min((int)p.ilen[b], (int)p.T);
   const int L = utt_labels(p, b);
   const int nwa = L / 32 + 1;  // warps that own at least one state (threads 0..L)

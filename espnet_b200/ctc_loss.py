@@ -208,12 +208,18 @@ class _Plan(object):
         [0,V) or equal to blank, or olen > lmax).  Synchronises the stream."""
         import ctypes
 
-        n = ctypes.c_int32(0)
+        return self.status()[0]
+
+    def status(self):
+        """(invalid utterances, utterances the log-domain sweeps had to redo) of the last call on this plan."""
+        import ctypes
+
+        n, r = ctypes.c_int32(0), ctypes.c_int32(0)
         with torch.cuda.device(self.logits.device):
             rc = _lib.load().b200_ctc_loss_status(self.ws_ptr, self.T, self.B, self.V, self.lmax, ctypes.byref(n),
-                                                  self.stream)
+                                                  ctypes.byref(r), self.stream)
         _lib.check(rc, "b200_ctc_loss_status")
-        return int(n.value)
+        return int(n.value), int(r.value)
 
 
 def _stream(device):

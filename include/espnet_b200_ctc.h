@@ -164,14 +164,21 @@ int b200_ctc_stage_labels(const int64_t* targets_host, int64_t n_targets,
                           const int64_t* ilen_host, const int64_t* olen_host, int64_t B,
                           int64_t* pinned_host, int64_t* dev, void* stream);
 
+/* Test hook: with on != 0, _fwd_bwd runs its lattice sweeps in the log domain only (the kernels that otherwise
+ * redo the utterances the float64 linear-domain sweeps cannot certify), so that the parity tests can exercise
+ * both.  Process-wide; returns the previous setting. */
+int b200_ctc_debug_force_log_sweep(int on);
+
 /* Number of utterances of the last _forward / _fwd_bwd call on `workspace` whose targets were
  * invalid: a label outside [0,V), a label equal to blank, or olen[b] > Lmax.  torch.nn.CTCLoss
  * raises for such input on the CPU (espnet2/asr/ctc.py:49 calls it); here the kernels clamp the
  * label / the length so that nothing is read or written out of bounds, give the utterance
  * nll = NaN and NaN gradient rows, and this call reports the count.  Synchronises `stream`
- * (one B-int device->host copy): meant for a debug / strict mode, not for every step. */
+ * (one B-int device->host copy): meant for a debug / strict mode, not for every step.
+ * n_redone_host (optional): utterances of a _fwd_bwd call whose lattice the float64 linear-domain sweeps could not
+ * certify (dynamic range) and which the log-domain sweeps therefore recomputed. */
 int b200_ctc_loss_status(const void* workspace, int64_t T, int64_t B, int64_t V, int64_t Lmax,
-                         int32_t* n_invalid_host, void* stream);
+                         int32_t* n_invalid_host, int32_t* n_redone_host /* may be NULL */, void* stream);
 
 /* grad_logits[t,b,:] *= gout[b] / expected (gout_n == B) or gout[0] / expected (gout_n == 1), in
  * place, for the autograd backward of a one-pass _fwd_bwd call whose upstream gradient was not

@@ -20,6 +20,18 @@ TOL_F32 = 1e-5
 TOL_BF16 = 1e-2
 
 
+@pytest.fixture(autouse=True, params=["lin", "log"])
+def sweep_domain(request):
+    """Every test of this file runs twice: with the float64 linear-domain lattice sweeps (the default; utterances
+    they cannot certify are redone in the log domain) and with the log-domain sweeps alone."""
+    from espnet_b200 import _lib
+
+    lib = _lib.load()
+    was = lib.b200_ctc_debug_force_log_sweep(1 if request.param == "log" else 0)
+    yield request.param
+    lib.b200_ctc_debug_force_log_sweep(was)
+
+
 def _run(x_btv, ilen, olen, ys, grad_scale=None, dtype=None, strided=True, split=False):
     """Returns (nll (B,) float64 numpy, grad (B,T,V) float64 numpy, loss_sum).
 

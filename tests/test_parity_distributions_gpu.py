@@ -25,7 +25,24 @@ TOL_F32, TOL_BF16 = 1e-5, 1e-2
 REPORT = os.path.join(ROOT, "gpurun_out", "parity_report.jsonl")
 
 
+@pytest.fixture(autouse=True, params=["lin", "log"])
+def sweep_domain(request):
+    """Every test of this file runs twice: with the float64 linear-domain lattice sweeps (the default; utterances
+    they cannot certify are redone in the log domain) and with the log-domain sweeps alone."""
+    from espnet_b200 import _lib
+
+    lib = _lib.load()
+    was = lib.b200_ctc_debug_force_log_sweep(1 if request.param == "log" else 0)
+    _domain[0] = request.param
+    yield request.param
+    lib.b200_ctc_debug_force_log_sweep(was)
+
+
+_domain = ["?"]
+
+
 def _report(**kw):
+    kw.setdefault("sweep", _domain[0])
     try:
         os.makedirs(os.path.dirname(REPORT), exist_ok=True)
         with open(REPORT, "a") as f:
@@ -140,6 +157,27 @@ def test_loss_c5_full_batch():
     assert _normrel(grad, rg) <= TOL_BF16
 
 
+def test_linear_sweeps_certify_ordinary_input_and_hand_over_the_rest(sweep_domain):
+    """The float64 linear-domain sweeps must carry ordinary posteriors (near-uniform, converged, a level change) by
+    themselves -- no utterance redone in the log domain -- and must hand saturated ones (N(0,1) x 30 logits: log-probs
+    hundreds of nats apart between frames) to the log-domain kernels rather than return what they could not certify."""
+    from espnet_b200 import ctc_loss as CL
+
+    if sweep_domain != "lin":
+        pytest.skip("linear-domain sweeps only")
+    redone = {}
+    for kind in ("randn", "trained", "level", "mismatch", "scale8", "scale30"):
+        c = _cases.make_loss_case_kind(kind, 8, 300, 512, 100, seed=350)
+        B, L = 8, c["ys"].shape[1]
+        xt = c["x"].cuda().transpose(0, 1)
+        plan = CL._Plan(xt, c["ys"].cuda().reshape(-1), torch.arange(B) * L, c["ilen"], c["olen"], L, 0)
+        CL.ctc_loss_fwd_bwd(xt, None, None, None, None, L, grad_scale=1.0 / B, plan=plan)
+        redone[kind] = plan.status()[1]
+    _report(test="redone_utterances", **redone)
+    assert redone["randn"] == 0 and redone["trained"] == 0 and redone["level"] == 0
+    assert redone["scale30"] > 0
+
+
 # ---------------------------------------------------------------------------------------------- prefix scores
 ATOL = 1e-4
 
@@ -161,6 +199,8 @@ def _close(got, ref, atol=ATOL, tag=None, ulps=2):
 
 
 def _walk_vs_reference_th(c, nsteps, snum=0, margin=0, seed=0, tag=None, follow=True):
+    if _domain[0] == "log":
+        pytest.skip("prefix scoring does not depend on the loss sweeps: run once")
     from espnet_b200.ctc_prefix_score import CTCPrefixScoreB200
     from tests._walk import walk_vs_reference_th
 
