@@ -6,7 +6,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libespnet_b200_ctc.so")
+# (B200_CTC_LIB: a developer build of the same library, e.g. one with -DB200_SWEEP_CLOCKS)
+LIB_PATH = os.environ.get("B200_CTC_LIB") or os.path.join(_HERE, "libespnet_b200_ctc.so")
 
 F32, BF16, F16 = 0, 1, 2
 LOGZERO = -10000000000.0

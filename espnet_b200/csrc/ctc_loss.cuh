@@ -52,7 +52,6 @@ struct LossWs {
   double* pd;       // [B][T][Kp]  2^(lpg + gff): the probabilities of blank / labels as doubles, scaled per frame
                     //             so that the largest of them is in [1, 2) (feed-forward scale)
   int* gff;         // [B][T]      that per-frame scale exponent (>= 0)
-  int* gcum;        // [2][B][T]   cumulative feed-forward exponent along each sweep direction, up to and incl. frame t
   int* gwarp;       // [2][B][ceil(T/8)][8]  block (warp) scale exponent of the sweep during chunk c:
                     //             true value = stored * 2^-(gcum + gwarp)
   int* gtot;        // [B]         sum over the frames of gff
@@ -90,7 +89,6 @@ inline LossWs carve_loss_ws(void* base, int64_t T, int64_t B, int64_t V, int64_t
   w.done = (int*)take(sizeof(int) * B);
   w.pd = (double*)take(sizeof(double) * B * T * w.Kp);
   w.gff = (int*)take(sizeof(int) * B * T);
-  w.gcum = (int*)take(sizeof(int) * 2 * B * T);
   w.gwarp = (int*)take(sizeof(int) * 2 * B * ((T + 7) / 8) * 8);
   w.gtot = (int*)take(sizeof(int) * B);
   w.redo = (int*)take(sizeof(int) * B);

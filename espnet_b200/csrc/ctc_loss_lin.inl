@@ -19,10 +19,14 @@
 // log-domain kernels (LossWs::redo), so the result never depends on the range being enough.
 namespace b200 {
 
-constexpr int kLinCHF = 8;      // frames per chunk
-constexpr int kLinSlots = 10;   // chunks of pd rows in shared memory
-constexpr int kLinAhead = 3;    // bulk copies run this many chunks ahead of warp 0
-constexpr int kLinR = 128;      // boundary ring, frames
+constexpr int kLinCHF = 8;        // frames per chunk
+constexpr int kLinMaxSlots = 32;  // chunks of pd rows in shared memory (as many as fit, see lin_slots)
+constexpr int kLinReady = 64;     // ring of "chunk staged" tags
+// The boundary ring (frames) must hold everything a warp can publish before its successor has read it.  A warp can
+// lead its successor by at most the row ring (the helper does not stage chunk s before EVERY warp has consumed chunk
+// s - nslots), so the ring is sized from nslots: 8 * (nslots + 2) frames rounded up to a power of two (lin_plan).
+// (With a fixed 128-frame ring and 20 row slots warp 0 -- which polls nobody and gains ~450 cycles per chunk on the
+// others -- overwrote records its successor had not read yet, and the successor waited forever.)
 
 // label state of lane 31 of a warp after frame `tag`, in that warp's block scale g
 struct __align__(16) BRec {
@@ -56,38 +60,59 @@ __device__ __forceinline__ int expo_field(int hi) { return (hi >> 20) & 0x7ff; }
 // v * 2^d for any integer d, by exponent arithmetic: zero / subnormal in, or a result below the normal range, gives 0
 __device__ __forceinline__ double scale_pow2(int lo, int hi, int d) {
   const int e = expo_field(hi);
-  int ne = e + d;
-  if (e == 0 || ne <= 0) return 0.0;
-  if (ne > 2046) ne = 2046;
-  return __hiloint2double((hi & 0x800fffff) | (ne << 20), lo);
+  const int ne = min(e + d, 2046);
+  const bool zero = (e == 0) | (ne <= 0);  // (selects, no branches: this sits in front of every chunk)
+  return __hiloint2double(zero ? 0 : ((hi & 0x800fffff) | (ne << 20)), zero ? 0 : lo);
 }
 __device__ __forceinline__ double pow2_double(int g) {  // |g| <= 1022
   return __hiloint2double((1023 + g) << 20, 0);
 }
 
 struct LinSmem {
-  BRec* bnd;       // [nw][kLinR]
-  int* ready;      // [32] chunk c staged (tag)
+  BRec* bnd;       // [nw][ring]
+  int* ready;      // [kLinReady] chunk c staged (tag)
   int* prog;       // [8]  last chunk whose rows state warp w has consumed
-  double* pd;      // [kLinSlots][CHF][Kp]
-  uint64_t* bar;   // [kLinSlots]
+  uint64_t* bar;   // [kLinMaxSlots]
+  double* pd;      // [nslots][CHF][Kp]
 };
 
-__device__ __forceinline__ LinSmem carve_lin_smem(unsigned char* base, int nw, int Kp) {
+__device__ __forceinline__ LinSmem carve_lin_smem(unsigned char* base, int nw, int ring) {
   LinSmem s;
   s.bnd = reinterpret_cast<BRec*>(base);
-  s.ready = reinterpret_cast<int*>(s.bnd + (size_t)nw * kLinR);
-  s.prog = s.ready + 32;
-  s.pd = reinterpret_cast<double*>(s.prog + 8 + 8);  // (keeps 16-byte alignment)
-  s.bar = reinterpret_cast<uint64_t*>(s.pd + (size_t)kLinSlots * kLinCHF * Kp);
+  s.ready = reinterpret_cast<int*>(s.bnd + (size_t)nw * ring);
+  s.prog = s.ready + kLinReady;
+  s.bar = reinterpret_cast<uint64_t*>(s.prog + 8);
+  s.pd = reinterpret_cast<double*>(s.bar + kLinMaxSlots);
   return s;
 }
-static size_t lin_smem_bytes(int nw, int64_t Kp) {
-  return sizeof(BRec) * (size_t)nw * kLinR + sizeof(int) * 48 + sizeof(double) * (size_t)kLinSlots * kLinCHF * (size_t)Kp +
-         sizeof(uint64_t) * kLinSlots;
+static size_t lin_smem_fixed(int nw, int ring) {
+  return sizeof(BRec) * (size_t)nw * ring + sizeof(int) * (kLinReady + 8) + sizeof(uint64_t) * kLinMaxSlots;
+}
+struct LinPlan {
+  int nslots, ring;
+  size_t smem;
+};
+// As many chunk slots as fit: the rows come from DRAM (~2 us) and a chunk lasts 8 frames x ~20 ns, so the copies must
+// run a dozen chunks ahead of the first warp; the most skewed warp is nw chunks behind it.  The boundary ring follows
+// from the slot count (see above): 256 frames serve up to 30 slots, 128 frames up to 14.
+static LinPlan lin_plan(int nw, int64_t Kp) {
+  const size_t slot = sizeof(double) * kLinCHF * (size_t)Kp;
+  LinPlan best{0, 128, 0};
+  const int rings[2] = {256, 128};
+  for (int ring : rings) {
+    const size_t fixed = lin_smem_fixed(nw, ring);
+    const size_t total = (size_t)max_smem_optin() - 4096;
+    if (fixed + slot > total) continue;
+    int64_t n = (int64_t)((total - fixed) / slot);
+    const int64_t cap = ring / kLinCHF - 2;
+    if (n > cap) n = cap;
+    if (n > kLinMaxSlots) n = kLinMaxSlots;
+    if (n > best.nslots) best = LinPlan{(int)n, ring, fixed + slot * (size_t)n};
+  }
+  return best;
 }
 
-__global__ void __launch_bounds__(288) ctc_sweep_lin_kernel(LossParams p) {
+__global__ void __launch_bounds__(288) ctc_sweep_lin_kernel(LossParams p, int nslots, int ring) {
   constexpr int CHF = kLinCHF;
   extern __shared__ __align__(16) unsigned char lin_smem[];
   const int d = blockIdx.y;
@@ -96,20 +121,22 @@ __global__ void __launch_bounds__(288) ctc_sweep_lin_kernel(LossParams p) {
   const int nw = (blockDim.x >> 5) - 1;  // state warps launched; warp nw is the helper
   const int Kp = (int)p.ws.Kp;
   const int64_t Sp = p.ws.Sp;
-  const LinSmem sm = carve_lin_smem(lin_smem, nw, Kp);
+  const LinSmem sm = carve_lin_smem(lin_smem, nw, ring);
+  const int rmask = ring - 1;
   __shared__ double s_finv[2];
   __shared__ int s_fing[2];
   __shared__ int s_gtot;
   __shared__ double s_zero;
+  __shared__ double s_bn[8][kLinCHF];  // boundary values of the chunk in the block's scale, per state warp
 
   // shared-memory set-up overlaps the tail of the previous kernels; after the wait the rows of the stream kernel
   // (pd, gff) and the results of the prep kernel (utterance order, labels) may be used
-  for (int k = i; k < nw * kLinR; k += blockDim.x) sm.bnd[k].tag = -1;
-  if (i < 32) sm.ready[i] = -1;
+  for (int k = i; k < nw * ring; k += blockDim.x) sm.bnd[k].tag = -1;
+  if (i < kLinReady) sm.ready[i] = -1;
   if (i < 8) sm.prog[i] = -1;
   if (i == 0) {
     s_zero = 0.0;
-    for (int k = 0; k < kLinSlots; ++k) mbar_init(&sm.bar[k], 1);
+    for (int k = 0; k < nslots; ++k) mbar_init(&sm.bar[k], 1);
     mbar_fence_init();
     fence_proxy_async();
   }
@@ -132,59 +159,61 @@ __global__ void __launch_bounds__(288) ctc_sweep_lin_kernel(LossParams p) {
   const int nchunk = (Tb + CHF - 1) / CHF;
   if (warp >= nwa && warp != nw) return;
   const int chunk_floats = CHF * Kp;  // doubles per slot
-  // frames of chunk c, and the slot row that holds logical frame 8c + j (beta: the rows arrive in physical order)
   auto frames_in = [&](int c) { return min(CHF, Tb - c * CHF); };
 
   if (warp == nw) {
-    // ------------------------------------------------------------------ helper warp: staging + gcum
+    // ------------------------------------------------------------------ helper warp: staging
     const double* pd_b = p.ws.pd + (int64_t)b * p.T * Kp;
-    const int* gff_b = p.ws.gff + (int64_t)b * p.T;
-    int* gcum_b = p.ws.gcum + ((int64_t)d * p.B + b) * p.T;
-    auto stage = [&](int c) {
+    // (chunks are staged and awaited in order: the slot indices are counted, not computed -- an integer division per
+    // chunk is ~40 dependent instructions)
+    int st_slot = 0, next_stage = 0;
+    auto stage = [&](int c) {  // lane 0
       const int n = frames_in(c);
-      const int slot = c % kLinSlots;
       const int prow = d ? (Tb - c * CHF - n) : c * CHF;  // first physical row of the chunk
       const uint32_t bytes = (uint32_t)(n * Kp * 8);
-      mbar_arrive_expect_tx(&sm.bar[slot], bytes);
-      bulk_g2s(sm.pd + (size_t)slot * chunk_floats, pd_b + (int64_t)prow * Kp, bytes, &sm.bar[slot]);
+      mbar_arrive_expect_tx(&sm.bar[st_slot], bytes);
+      bulk_g2s(sm.pd + (size_t)st_slot * chunk_floats, pd_b + (int64_t)prow * Kp, bytes, &sm.bar[st_slot]);
     };
-    if (lane == 0)
-      for (int c = 0; c < kLinAhead && c < nchunk; ++c) stage(c);
-    int run = 0;  // cumulative feed-forward exponent before this chunk
-    for (int c = 0; c < nchunk; ++c) {
-      const int n = frames_in(c);
-      mbar_wait(&sm.bar[c % kLinSlots], (uint32_t)((c / kLinSlots) & 1));
-      if (lane == 0) sts_volatile_s32(&sm.ready[c & 31], c);
-      // cumulative scale up to and including each frame of the chunk, in sweep order
-      {
-        const int f = c * CHF + lane;          // logical frame of this lane
-        const int t = d ? (Tb - 1 - f) : f;    // physical frame
-        int g = (lane < n) ? gff_b[t] : 0;
-#pragma unroll
-        for (int o = 1; o < CHF; o <<= 1) {
-          const int u = __shfl_up_sync(0xffffffffu, g, o);
-          if (lane >= o) g += u;
-        }
-        if (lane < n) gcum_b[t] = run + g;
-        run += __shfl_sync(0xffffffffu, g, n - 1);
-      }
-      // the slot of chunk c + kLinAhead is free once every state warp has consumed chunk c + kLinAhead - kLinSlots
-      const int nx = c + kLinAhead;
-      if (nx < nchunk) {
-        const int need = nx - kLinSlots;
+    // stage every chunk whose slot is free: chunk s replaces chunk s - nslots, which every state warp must have
+    // consumed.  Never sleeps (__nanosleep costs about a microsecond, three chunks of the sweep): the copies run as far
+    // ahead as the ring allows, so this only spins when the ring is full, and then there is nothing else to do.
+    auto stage_free = [&](bool must) {
+      for (;;) {
+        if (next_stage >= nchunk) return;
+        const int need = next_stage - nslots;
         if (need >= 0) {
-          for (;;) {
-            const int pr = (lane < nwa) ? lds_volatile_s32(&sm.prog[lane]) : 0x7fffffff;
-            if (__all_sync(0xffffffffu, pr >= need)) break;
-            __nanosleep(64);
+          const int pr = (lane < nwa) ? lds_volatile_s32(&sm.prog[lane]) : 0x7fffffff;
+          if (!__all_sync(0xffffffffu, pr >= need)) {
+            if (must) continue;
+            return;
           }
         }
-        if (lane == 0) stage(nx);
+        if (lane == 0) stage(next_stage);
+        st_slot = (st_slot + 1 == nslots) ? 0 : st_slot + 1;
+        ++next_stage;
+        must = false;
       }
+    };
+    stage_free(false);
+    int w_slot = 0;
+    uint32_t w_par = 0;
+    for (int c = 0; c < nchunk; ++c) {
+      if (next_stage <= c) stage_free(true);  // (cannot happen with nslots > nw + 2, kept for safety)
+      mbar_wait(&sm.bar[w_slot], w_par);
+      if (++w_slot == nslots) { w_slot = 0; w_par ^= 1u; }
+      if (lane == 0) sts_volatile_s32(&sm.ready[c & (kLinReady - 1)], c);
+      stage_free(false);
+    }
+    // sum of the feed-forward exponents of the utterance (enters log p(y|x) and the occupancy kernel's reference level)
+    int gsum = 0;
+    {
+      const int* gff_b = p.ws.gff + (int64_t)b * p.T;
+      for (int t = lane; t < Tb; t += 32) gsum += gff_b[t];
+      gsum = __reduce_add_sync(0xffffffffu, gsum);
     }
     if (lane == 0) {
-      s_gtot = run;
-      if (d == 0) p.ws.gtot[b] = run;
+      s_gtot = gsum;
+      if (d == 0) p.ws.gtot[b] = gsum;
     }
     asm volatile("bar.sync 1, %0;" ::"r"((nwa + 1) * 32) : "memory");
     return;
@@ -200,8 +229,8 @@ __global__ void __launch_bounds__(288) ctc_sweep_lin_kernel(LossParams p) {
   const int kcol = has_label ? 1 + pi : 0;
   const bool lane0 = lane == 0, lane31 = lane == 31;
   const bool poll = warp > 0;
-  const BRec* bsrc = sm.bnd + (size_t)(poll ? warp - 1 : 0) * kLinR;
-  BRec* bdst = sm.bnd + (size_t)warp * kLinR;
+  const BRec* bsrc = sm.bnd + (size_t)(poll ? warp - 1 : 0) * ring;
+  BRec* bdst = sm.bnd + (size_t)warp * ring;
   int* outp = reinterpret_cast<int*>(p.ws.lat) + (((int64_t)d * p.B + b) * p.T + (d ? (Tb - 1) : 0)) * Sp + 2 * i;
   const int64_t ostep = d ? -Sp : Sp;
   int* gw_out = p.ws.gwarp + (((int64_t)d * p.B + b) * ((p.T + 7) / 8)) * 8 + warp;
@@ -210,66 +239,79 @@ __global__ void __launch_bounds__(288) ctc_sweep_lin_kernel(LossParams p) {
 
   double ab = 0.0, al = 0.0;
   int Gw = 0;
+  int ld_slot = 0;  // slot of the next chunk to load (chunks are loaded in order)
+  const uint32_t row_bytes = (uint32_t)(Kp * 8), slot_bytes = (uint32_t)(chunk_floats * 8);
+  const uint32_t row_step = d ? (uint32_t)(-(int)row_bytes) : row_bytes;
+  const uint32_t col_off = (uint32_t)(kcol * 8);
 
   // probabilities of chunk c for this thread: blank column and own label column, frames in logical order
   auto load_chunk = [&](int c, double(&xb)[CHF], double(&xl)[CHF]) {
-    while (lds_volatile_s32(&sm.ready[c & 31]) != c) { }
+    while (lds_volatile_s32(&sm.ready[c & (kLinReady - 1)]) != c) { }
     const int n = frames_in(c);
-    const uint32_t base = a_pd + (uint32_t)((c % kLinSlots) * chunk_floats * 8);
+    // logical frame j of the chunk sits in slot row j (alpha) or n - 1 - j (beta: the rows arrive in physical order)
+    uint32_t row = a_pd + (uint32_t)ld_slot * slot_bytes + (d ? (uint32_t)(n - 1) * row_bytes : 0u);
+    ld_slot = (ld_slot + 1 == nslots) ? 0 : ld_slot + 1;
 #pragma unroll
     for (int f = 0; f < CHF; ++f) {
-      const int j = min(f, n - 1);
-      const uint32_t row = base + (uint32_t)((d ? (n - 1 - j) : j) * Kp * 8);
       xb[f] = lds_f64(row);
-      xl[f] = lds_f64(has_label ? row + (uint32_t)(kcol * 8) : a_zero);
+      xl[f] = lds_f64(has_label ? row + col_off : a_zero);
+      if (f < n - 1) row += row_step;
     }
   };
 
-  auto run_chunk = [&](int c, const double(&xb)[CHF], const double(&xl)[CHF]) {
-    const int n = frames_in(c);
+  // FULL: a chunk of 8 frames that is not the first one -- straight-line code, no branch inside the frames
+  auto run_chunk = [&](auto full_tag, int c, const double(&xb)[CHF], const double(&xl)[CHF]) {
+    constexpr bool FULL = decltype(full_tag)::value;
+    const int n = FULL ? CHF : frames_in(c);
     const int f0 = c * CHF;
-    const int j0 = (c == 0) ? 1 : 0;
+    const int j0 = (!FULL && c == 0) ? 1 : 0;
     if (lane0) sts_volatile_s32(&sm.prog[warp], c);  // (the rows of chunk c are in registers)
-    // boundary records of frames f0 + j - 1 for j in [j0, n): the last one is published last
-    BRec br[CHF];
-#pragma unroll
-    for (int f = 0; f < CHF; ++f) { br[f].lo = 0; br[f].hi = 0; br[f].tag = 0; br[f].g = 0; }
+    // Boundary records of frames f0 + j - 1 for j in [j0, n): LANE j reads record j (one load for the warp; the last
+    // one is published last), contributes it to the level of the block, converts it to the block's new scale, and
+    // leaves it in shared memory for lane 0.  Doing this per lane instead of eight times in every lane keeps the
+    // front of a chunk short.
+    BRec r;
+    r.lo = 0; r.hi = 0; r.tag = 0; r.g = 0;
+    const bool mine = poll && lane >= j0 && lane < n;  // this lane holds a record
     if (poll && n > j0) {
-      const int last = f0 + n - 2;
-      BRec r;
-      do { r = lds_brec(&bsrc[last & (kLinR - 1)]); } while (r.tag != last);
-#pragma unroll
-      for (int f = 0; f < CHF; ++f) {
-        const int fr = f0 + f - 1;
-        if (f >= j0 && f < n) br[f] = lds_brec(&bsrc[fr & (kLinR - 1)]);
+      const BRec* src = &bsrc[(f0 + lane - 1) & rmask];
+      const int want = f0 + lane - 1;
+      for (;;) {
+        if (mine) r = lds_brec(src);
+        if (__all_sync(0xffffffffu, !mine || r.tag == want)) break;
       }
     }
     // ---- feedback scale of this block for the chunk: own states and what will flow in, to ~1
-    if (c > 0) {
+    if (FULL || c > 0) {
+      const int er = expo_field(r.hi);
+      const int cand = (mine && er != 0) ? er + (Gw - r.g) : 0;
       const int hown = max(__double2hiint(ab), __double2hiint(al));  // non-negative doubles order like their high words
-      int lev = expo_field(__reduce_max_sync(0xffffffffu, hown));
-      if (poll) {
-#pragma unroll
-        for (int f = 0; f < CHF; ++f) {
-          const int e = expo_field(br[f].hi);
-          if (f < n && e != 0) lev = max(lev, e + (Gw - br[f].g));
-        }
-      }
-      int g = 0;
-      if (lev != 0) g = max(min(1023 - lev, 1000), -1000);
-      if (g != 0) {
-        const double sc = pow2_double(g);
-        ab *= sc;
-        al *= sc;
-        Gw += g;
-      }
+      const int lev = __reduce_max_sync(0xffffffffu, max(expo_field(hown), cand));
+      // Upward the step is capped (the rest follows in the next chunk).  DOWNWARD it is not: when a value arrives
+      // from the previous block that is thousands of binades above this block's own states (a block whose junk has
+      // decayed for many chunks, rescaled to 1 every time, and which the alignment now enters), the block must take
+      // the incoming scale at once -- its own states are then below 2^-1022 of it and flush to zero, legitimately.
+      // (A cap of -1000 here saturated the incoming value instead: garbage that the certificate could not see.)
+      const int g = (lev != 0) ? min(1023 - lev, 1000) : 0;
+      const double sc = (g >= -1000) ? pow2_double(g) : 0.0;
+      ab *= sc;
+      al *= sc;
+      Gw += g;
     }
     if (lane0) gw_out[(int64_t)c * 8] = Gw;
     double bn[CHF];
+    if (poll) {
+      if (lane < CHF) s_bn[warp][lane] = mine ? scale_pow2(r.lo, r.hi, Gw - r.g) : 0.0;
+      __syncwarp();
 #pragma unroll
-    for (int f = 0; f < CHF; ++f) bn[f] = poll ? scale_pow2(br[f].lo, br[f].hi, Gw - br[f].g) : 0.0;
+      for (int f = 0; f < CHF; ++f) bn[f] = s_bn[warp][f];
+      __syncwarp();
+    } else {
+#pragma unroll
+      for (int f = 0; f < CHF; ++f) bn[f] = 0.0;
+    }
 
-    if (c == 0) {
+    if (!FULL && c == 0) {
       // frame 0: only the first blank and the first label are reachable
       if (i == 0) { ab = xb[0]; al = xl[0]; }
       if (lane31) sts_brec(&bdst[0], al, 0, Gw);
@@ -278,7 +320,7 @@ __global__ void __launch_bounds__(288) ctc_sweep_lin_kernel(LossParams p) {
     }
 #pragma unroll
     for (int f = 0; f < CHF; ++f) {
-      if (f >= j0 && f < n) {
+      if (FULL || (f >= j0 && f < n)) {
         const int fr = f0 + f;
         const int slo = __shfl_up_sync(0xffffffffu, __double2loint(al), 1);
         const int shi = __shfl_up_sync(0xffffffffu, __double2hiint(al), 1);
@@ -289,11 +331,15 @@ __global__ void __launch_bounds__(288) ctc_sweep_lin_kernel(LossParams p) {
         const double nab = xb[f] * (ab + nbr);
         al = nal;
         ab = nab;
-        if (lane31) sts_brec(&bdst[fr & (kLinR - 1)], al, fr, Gw);
+        if (lane31) sts_brec(&bdst[fr & rmask], al, fr, Gw);
         if (active) *reinterpret_cast<int2*>(outp) = make_int2(__double2hiint(ab), __double2hiint(al));
         outp += ostep;
       }
     }
+  };
+  auto run = [&](int c, const double(&xb)[CHF], const double(&xl)[CHF]) {
+    if (c > 0 && frames_in(c) == CHF) run_chunk(std::true_type{}, c, xb, xl);
+    else run_chunk(std::false_type{}, c, xb, xl);
   };
 
   {
@@ -302,10 +348,10 @@ __global__ void __launch_bounds__(288) ctc_sweep_lin_kernel(LossParams p) {
     int c = 0;
     while (c < nchunk) {
       if (c + 1 < nchunk) load_chunk(c + 1, xb1, xl1);
-      run_chunk(c, xb0, xl0);
+      run(c, xb0, xl0);
       if (++c >= nchunk) break;
       if (c + 1 < nchunk) load_chunk(c + 1, xb0, xl0);
-      run_chunk(c, xb1, xl1);
+      run(c, xb1, xl1);
       ++c;
     }
   }
@@ -336,18 +382,20 @@ __global__ void __launch_bounds__(288) ctc_sweep_lin_kernel(LossParams p) {
 }
 
 static int launch_sweep_lin(const LossParams& p, cudaStream_t st, bool pdl) {
-  const int threads = (int)align_up((size_t)(p.Lmax + 1), 32) + 32;  // + the helper warp
-  size_t smem = lin_smem_bytes(threads / 32 - 1, p.ws.Kp);
-  if (2 * (p.b1 - p.b0) <= num_sms() && smem < 116 * 1024) smem = 116 * 1024;  // one latency chain per SM
+  const int nw = (int)(align_up((size_t)(p.Lmax + 1), 32) / 32);
+  const int threads = (nw + 1) * 32;  // + the helper warp
+  const LinPlan pl = lin_plan(nw, p.ws.Kp);
   auto kern = ctc_sweep_lin_kernel;
-  if (smem > 48 * 1024) B200_CUDA(set_max_smem_cached((const void*)kern, (int)smem));
-  B200_CUDA(launch_kernel(kern, dim3((unsigned)(p.b1 - p.b0), 2), dim3(threads), smem, st, pdl, p));
+  B200_CUDA(set_max_smem_cached((const void*)kern, (int)pl.smem));
+  B200_CUDA(launch_kernel(kern, dim3((unsigned)(p.b1 - p.b0), 2), dim3(threads), pl.smem, st, pdl, p, pl.nslots, pl.ring));
   return B200_OK;
 }
 
-// the linear sweep serves label sequences of up to 255 (8 state warps) whose staged rows fit shared memory
+// the linear sweep serves label sequences of up to 255 (8 state warps) whose staged rows leave room for a deep ring
 static bool lin_sweep_ok(const LossParams& p) {
-  return p.Lmax + 1 <= 256 && lin_smem_bytes((int)(align_up((size_t)(p.Lmax + 1), 32) / 32), p.ws.Kp) <= (size_t)max_smem_optin() - 2048;
+  if (p.Lmax + 1 > 256) return false;
+  const int nw = (int)(align_up((size_t)(p.Lmax + 1), 32) / 32);
+  return lin_plan(nw, p.ws.Kp).nslots >= nw + 4;
 }
 
 }  // namespace b200

@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
   const int chunk = (tot + total_warps * split - 1) / (total_warps * split);
   for (;;) {
   int ticket = 0;
-  if (lane == 0) ticket = atomicAdd(p.ws.bad + 5, 1);
+  if (lane == 0) ticket = atomicAdd(p.ws.bad + (p.redo_mode ? 7 : 5), 1);
   ticket = __shfl_sync(0xffffffffu, ticket, 0);
   const int r0 = min(ticket * chunk, tot);
   const int n = min(r0 + chunk, tot) - r0;
@@ -217,7 +217,8 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
       const int ea = wa >> 20, eb = wb >> 20;
       if (ea == 0 || eb == 0) {
         if ((ea == 0 && reach_a) || (eb == 0 && reach_b)) {
-          const int c = (ea ? ea : -51) + (eb ? eb : -51) - ga - gb - kt + 1 - (int)floorf(lp);
+          // (a word with exponent field 0 is a zero OR a subnormal: anything below 2^-1022, i.e. field 1)
+          const int c = (ea ? ea : 1) + (eb ? eb : 1) - ga - gb - kt + 1 - (int)floorf(lp);
           cert = max(cert, c);
         }
         return -3.0e38f;
@@ -276,7 +277,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
         // a 32-byte sector fill and write-back in DRAM.
         const T with = ElemTraits<T>::from_float(wgt * (pk - o * inv));
         const T without = ElemTraits<T>::from_float(wgt * pk);
-        if (raw_bits(with) != raw_bits(without))
+        if (raw_bits(with) != raw_bits(without) || p.redo_mode)  // (redo pass: the first pass may have patched it)
           grad[(int64_t)b * p.gstride_b + (int64_t)t * p.gstride_t + s_lab[k]] = with;
       } else {
         out[1 + k] = pk - o * inv;

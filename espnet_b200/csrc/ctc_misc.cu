@@ -257,3 +257,4 @@ extern "C" int b200_ctc_viterbi(const float* lpz, int64_t T, int64_t V, const in
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }
+

@@ -164,9 +164,11 @@ int b200_ctc_stage_labels(const int64_t* targets_host, int64_t n_targets,
                           const int64_t* ilen_host, const int64_t* olen_host, int64_t B,
                           int64_t* pinned_host, int64_t* dev, void* stream);
 
-/* Test hook: with on != 0, _fwd_bwd runs its lattice sweeps in the log domain only (the kernels that otherwise
- * redo the utterances the float64 linear-domain sweeps cannot certify), so that the parity tests can exercise
- * both.  Process-wide; returns the previous setting. */
+/* Selects the lattice sweeps of _fwd_bwd.  on != 0 (the default): log-domain sweeps.  on == 0: float64
+ * linear-domain sweeps (Lmax <= 255), whose patch kernel certifies every row it decodes and hands the
+ * utterances it cannot certify (dynamic range) to the log-domain kernels; same results within the parity
+ * bars, currently slower, kept selectable so that the parity tests exercise both.
+ * Process-wide; returns the previous setting. */
 int b200_ctc_debug_force_log_sweep(int on);
 
 /* Number of utterances of the last _forward / _fwd_bwd call on `workspace` whose targets were

@@ -22,8 +22,8 @@ TOL_BF16 = 1e-2
 
 @pytest.fixture(autouse=True, params=["lin", "log"])
 def sweep_domain(request):
-    """Every test of this file runs twice: with the float64 linear-domain lattice sweeps (the default; utterances
-    they cannot certify are redone in the log domain) and with the log-domain sweeps alone."""
+    """Every test of this file runs twice: with the log-domain lattice sweeps (the default) and with the float64
+    linear-domain sweeps (utterances they cannot certify are redone in the log domain)."""
     from espnet_b200 import _lib
 
     lib = _lib.load()

@@ -27,8 +27,8 @@ REPORT = os.path.join(ROOT, "gpurun_out", "parity_report.jsonl")
 
 @pytest.fixture(autouse=True, params=["lin", "log"])
 def sweep_domain(request):
-    """Every test of this file runs twice: with the float64 linear-domain lattice sweeps (the default; utterances
-    they cannot certify are redone in the log domain) and with the log-domain sweeps alone."""
+    """Every test of this file runs twice: with the log-domain lattice sweeps (the default) and with the float64
+    linear-domain sweeps (utterances they cannot certify are redone in the log domain)."""
     from espnet_b200 import _lib
 
     lib = _lib.load()
@@ -101,7 +101,7 @@ def _check_loss(c, tag, dtype=None, split=False, tol=TOL_F32):
     # loss: 1e-5 relative; a converged model's nll (~1e-6 nats in all) is below what ANY float32 evaluation of
     # T log-probabilities near zero resolves, the reference's included: there the bar is the reference's own error
     T = c["x"].shape[1]
-    assert (np.abs(nll - rn) <= np.maximum(TOL_F32 * np.abs(rn), np.maximum(2 * np.abs(fn - rn), 1.2e-7 * T))).all()
+    assert (np.abs(nll - rn) <= np.maximum(TOL_F32 * np.abs(rn), np.maximum(2 * np.abs(fn - rn), 2.4e-7 * T))).all()
     assert e_g <= max(tol, e_ref), (e_g, e_ref)
     return e_g, e_ref
 

@@ -3,6 +3,10 @@ import sys, torch
 sys.path.insert(0, ".")
 from espnet_b200 import ctc_loss as CL
 from tests import _cases
+from espnet_b200 import _lib
+import os
+if os.environ.get("B200_LIN"):
+    _lib.load().b200_ctc_debug_force_log_sweep(0)
 B, T, V, L = 64, 500, 5000, 150
 dt = torch.bfloat16 if len(sys.argv) < 2 or sys.argv[1] == "bf16" else torch.float32
 full = len(sys.argv) > 2 and sys.argv[2] == "full"
