@@ -9,6 +9,8 @@
 //                     first maximum kept, including its wrap-around read of state -1 for s = 0.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace b200 {
 
 // ------------------------------------------------------------------------------ greedy
@@ -258,3 +260,51 @@ extern "C" int b200_ctc_viterbi(const float* lpz, int64_t T, int64_t V, const in
   return B200_OK;
 }
 
+// ------------------------------------------------------------------------------ Viterbi without caller scratch
+// b200_ctc_viterbi_static: the same alignment with the back-pointer table in a file-scope device array instead of a
+// caller-allocated work buffer, for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that
+// forbid cudaMalloc).  No counterpart in the reference.
+//   * the array costs B200_CTC_VITERBI_STATIC_BYTES of device memory on EVERY GPU that loads the library, until exit;
+//   * in host code `g_vit_scratch` is a host-side stand-in, not a device address: the address a kernel can use comes
+//     from cudaGetSymbolAddress, fetched once per device with that device current and kept here;
+//   * every call on a device shares the array: calls that overlap on the GPU (two streams) race.  Nothing in it has
+//     to start at zero -- the kernel writes every back-pointer of frames 1..T-1 before the back-trace reads them --
+//     so what the previous call left behind is simply overwritten.
+static __device__ __align__(256) unsigned char g_vit_scratch[B200_CTC_VITERBI_STATIC_BYTES];
+
+namespace {
+std::mutex g_vit_mu;
+void* g_vit_ptr[64] = {nullptr};
+}  // namespace
+
+static int vit_static_ptr(void** out) {
+  int dev = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_CHECK_ARG(dev >= 0 && dev < 64, B200_ERR_INVALID_ARGUMENT, "device index %d outside [0,64)", dev);
+  std::lock_guard<std::mutex> lk(g_vit_mu);
+  if (g_vit_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    B200_CUDA(cudaGetSymbolAddress((void**)&ptr, g_vit_scratch));  // (the current device's instance of the array)
+    B200_CHECK_ARG(ptr != nullptr, B200_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+    g_vit_ptr[dev] = ptr;
+  }
+  *out = g_vit_ptr[dev];
+  return B200_OK;
+}
+
+extern "C" size_t b200_ctc_viterbi_static_max_bytes(void) { return (size_t)B200_CTC_VITERBI_STATIC_BYTES; }
+
+extern "C" int b200_ctc_viterbi_static(const float* lpz, int64_t T, int64_t V, const int64_t* y, int64_t L, int blank,
+                                       int64_t* align, void* stream) {
+  B200_CHECK_ARG(T >= 1 && L >= 0, B200_ERR_INVALID_ARGUMENT, "need T>=1, L>=0, got T=%lld L=%lld", (long long)T,
+                 (long long)L);
+  const size_t need = b200_ctc_viterbi_work_bytes(T, L);
+  B200_CHECK_ARG(need <= (size_t)B200_CTC_VITERBI_STATIC_BYTES, B200_ERR_UNSUPPORTED_SHAPE,
+                 "T=%lld, L=%lld need %zu bytes of back-pointers, the static scratch holds %zu: use b200_ctc_viterbi "
+                 "with a caller-allocated work buffer",
+                 (long long)T, (long long)L, need, (size_t)B200_CTC_VITERBI_STATIC_BYTES);
+  void* work = nullptr;
+  const int rc = vit_static_ptr(&work);
+  if (rc) return rc;
+  return b200_ctc_viterbi(lpz, T, V, y, L, blank, align, work, (size_t)B200_CTC_VITERBI_STATIC_BYTES, stream);
+}

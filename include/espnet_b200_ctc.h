@@ -276,6 +276,21 @@ int b200_ctc_viterbi(const float* lpz, int64_t T, int64_t V,
                      const int64_t* y, int64_t L, int blank,
                      int64_t* align, void* work, size_t work_bytes, void* stream);
 
+/* b200_ctc_viterbi without a caller-allocated work buffer.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  The back-pointer table lives in a
+ * file-scope device array of B200_CTC_VITERBI_STATIC_BYTES (4 MiB) that every GPU loading the library
+ * holds until exit; the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ * Limit: T * (2L+1) * 2 bytes <= B200_CTC_VITERBI_STATIC_BYTES (e.g. T=2000 with L<=523), else
+ * B200_ERR_UNSUPPORTED_SHAPE.  All calls on a device share the array: calls that overlap on the GPU
+ * (different streams) race; nothing in it needs clearing between calls.  Inputs, outputs and results are
+ * those of b200_ctc_viterbi. */
+#define B200_CTC_VITERBI_STATIC_BYTES (4u << 20)
+size_t b200_ctc_viterbi_static_max_bytes(void);
+int b200_ctc_viterbi_static(const float* lpz, int64_t T, int64_t V,
+                            const int64_t* y, int64_t L, int blank,
+                            int64_t* align, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
