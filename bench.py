@@ -392,8 +392,8 @@ def run_b200(args, rank, world, local_rank):
             return loss.detach()
         # trainer.py:384-397: (loss * weight).sum(); all-reduce of the statistic and of the weight; loss /= weight;
         # loss *= world_size -- every step, before backward
-        mean = exchange.step(loss.detach() * Bn)
-        (loss * exchange.scale()).backward()
+        mean = exchange.step(loss.detach(), float(Bn))
+        loss.backward(gradient=exchange.scale())
         return mean
 
     def sync_all():

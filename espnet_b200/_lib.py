@@ -41,6 +41,8 @@ SIGNATURES = {
     "b200_ctc_greedy": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _vp]),
     "b200_ctc_viterbi_work_bytes": (_sz, [_i64, _i64]),
     "b200_ctc_viterbi": (_int, [_vp, _i64, _i64, _vp, _i64, _int, _vp, _vp, _sz, _vp]),
+    "b200_peer_exchange_ring_floats": (_sz, [_i64]),
+    "b200_peer_sum_exchange": (_int, [_vp, _i64, _i64, _i64, _vp, _f32, _f32, _vp, _vp, _vp]),
     "b200_ctc_viterbi_static_max_bytes": (_sz, []),
     "b200_ctc_viterbi_static": (_int, [_vp, _i64, _i64, _vp, _i64, _int, _vp, _vp]),
 }

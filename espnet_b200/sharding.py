@@ -88,7 +88,7 @@ class StepLossExchange:
         self.device, self.group = torch.device(device), group
         self.n_utt = float(n_utt)
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
-        self.buf = torch.zeros(2, dtype=torch.float32, device=self.device)
+        self.buf = torch.zeros(4, dtype=torch.float32, device=self.device)  # total sum, total count, mean, scale
         self.peer = None
         self.transport = "none" if self.world == 1 else "allreduce"
         if self.world > 1 and transport in ("auto", "peer") and self.device.type == "cuda":
@@ -102,17 +102,25 @@ class StepLossExchange:
                     raise
                 self.why_not_peer = f"{type(e).__name__}: {e}"[:200]
 
-    def step(self, local_sum):
-        """local_sum: this rank's sum of nll (0-dim or 1-element device tensor).  Returns the global mean loss
-        (0-dim tensor); the global utterance count is left in ``self.buf[1]``."""
-        self.buf[0:1].copy_(local_sum.reshape(1))
-        self.buf[1] = self.n_utt
+    def step(self, local_sum, sum_scale=1.0):
+        """local_sum * sum_scale: this rank's sum of nll (0-dim or 1-element device tensor x host number, e.g. the
+        module's mean loss and B).  Returns the global mean loss (0-dim view, no kernel on the peer transport); the
+        totals are left in ``self.buf[0:2]``."""
         if self.peer is not None:
-            self.peer.exchange(self.buf)
-        elif self.world > 1:
-            dist.all_reduce(self.buf, op=dist.ReduceOp.SUM, group=self.group)
-        return self.buf[0] / self.buf[1]
+            ls = local_sum if local_sum.dtype == torch.float32 else local_sum.float()
+            self.peer.exchange(ls, sum_scale, self.n_utt, self.buf)
+            return self.buf[2]
+        self.buf[0:1].copy_(local_sum.reshape(1))
+        if sum_scale != 1.0:
+            self.buf[0:1].mul_(sum_scale)
+        self.buf[1] = self.n_utt
+        if self.world > 1:
+            dist.all_reduce(self.buf[0:2], op=dist.ReduceOp.SUM, group=self.group)
+        self.buf[2] = self.buf[0] / self.buf[1]
+        self.buf[3] = (self.n_utt * self.world) / self.buf[1]
+        return self.buf[2]
 
     def scale(self):
-        """n_utt * world / (global utterance count), as a 0-dim device tensor (no host synchronisation)."""
-        return (self.n_utt * self.world) / self.buf[1]
+        """n_utt * world / (global utterance count) as a 0-dim device tensor (no host synchronisation): pass it as
+        ``loss.backward(gradient=exchange.scale())``."""
+        return self.buf[3]

@@ -276,6 +276,26 @@ int b200_ctc_viterbi(const float* lpz, int64_t T, int64_t V,
                      const int64_t* y, int64_t L, int blank,
                      int64_t* align, void* work, size_t work_bytes, void* stream);
 
+/* ------------------------------------------------------------------------
+ * Per-step loss exchange between the GPUs of one box
+ * ------------------------------------------------------------------------
+ * Replaces, for the (sum of nll, number of utterances) pair, the all-reduces of
+ * espnet2/torch_utils/recursive_op.py:24,50 that espnet2/train/trainer.py:386-393 issues every iteration.
+ * ring_ptrs_host[r] (HOST array of `world` device addresses): rank r's slot ring of
+ * b200_peer_exchange_ring_floats(world) floats in peer-accessible (symmetric) memory, zeroed before the first
+ * call.  local_sum * sum_scale: this rank's sum of nll (local_sum: device fp32, e.g. the loss_sum output of
+ * b200_ctc_loss_fwd_bwd or the module's mean loss with sum_scale = B); local_count: this rank's number of
+ * utterances.  pair: fp32 (4,) device buffer out: [0] total sum, [1] total count (summed in rank order: bitwise
+ * identical on every rank), [2] global mean = [0]/[1], [3] local_count * world / [1] (what trainer.py:392-397's
+ * "loss /= weight; loss *= world_size" multiplies the local mean loss by before backward).  seq: 1, 2, 3, ... the same on every rank for
+ * the same step.  One kernel launch: peer
+ * stores of the pair + sequence number into every ring, then a bounded wait (~2 s) on the local ring; if a
+ * peer never arrives the totals are NaN and *status (device int32, may be NULL) is set to 1. */
+size_t b200_peer_exchange_ring_floats(int64_t world);
+int b200_peer_sum_exchange(const uint64_t* ring_ptrs_host, int64_t world, int64_t rank, int64_t seq,
+                           const float* local_sum, float sum_scale, float local_count,
+                           float* pair, int32_t* status, void* stream);
+
 /* b200_ctc_viterbi without a caller-allocated work buffer.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot allocate device memory (code under CUDA graph
  * capture, tight serving loops, harnesses that forbid cudaMalloc).  The back-pointer table lives in a

@@ -189,9 +189,19 @@ def test_reference_beam_search_single_hypothesis_path(name):
     from espnet.nets.scorers.ctc import CTCPrefixScorer as RefScorer
 
     want, _ = _reference_search(name, "BeamSearch", RefScorer(_toy.LogSoftmaxCTC(), cfg_eos(name)), torch.device("cuda"))
-    assert [h.yseq.tolist() for h in nbest] == [h.yseq.tolist() for h in want]
-    for a, b in zip(nbest, want):
-        assert abs(float(a.score) - float(b.score)) <= 1e-4 * len(a.yseq)
+    got_y, want_y = [h.yseq.tolist() for h in nbest], [h.yseq.tolist() for h in want]
+    if "near_tie" in name:
+        # The twin pairs are ~1e-5 apart.  Among the real hypotheses (scores of a few units, float32 spacing 2e-7) that
+        # is ~40 spacings and the order is well defined: token for token.  In the junk tail of the list (scores below
+        # -100, spacing 1.5e-5) the same gap is ONE spacing, i.e. rounding noise in any implementation: same set there.
+        k = sum(1 for h in want if float(h.score) > -50.0)
+        assert k >= 2 and got_y[:k] == want_y[:k]
+        assert sorted(got_y) == sorted(want_y)
+    else:
+        assert got_y == want_y
+    by_seq = {tuple(h.yseq.tolist()): float(h.score) for h in want}
+    for a in nbest:
+        assert abs(float(a.score) - by_seq[tuple(a.yseq.tolist())]) <= 1e-4 * len(a.yseq)
     if "near_tie" not in name:
         # and the n-best the reference recorded on the CPU.  (Not for the near-tie case: the reference's own search
         # orders a twin pair differently on a CUDA device than on the CPU -- tools/dev_neartie.py shows it with the

@@ -130,3 +130,49 @@ def test_ledger_without_process_group_is_local():
     assert led.slot(4).data_ptr() == led.slot(1).data_ptr()
     with pytest.raises(ValueError):
         LossLedger(0, 1, torch.device("cpu"))
+
+
+def _worker_step(rank, world, port, q):
+    """StepLossExchange with the all-reduce transport: what trainer.py:386-397 does every iteration."""
+    from espnet_b200.sharding import StepLossExchange
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    n_utt = 3 + rank                       # unequal shards: the backward scale is not 1
+    ex = StepLossExchange(torch.device("cpu"), n_utt=n_utt)
+    out = []
+    for step in range(3):
+        local = torch.tensor(10.0 * (step + 1) + rank)
+        mean = ex.step(local)
+        out.append((float(mean), float(ex.buf[1]), float(ex.scale())))
+    q.put((rank, ex.transport, out))
+    dist.destroy_process_group()
+
+
+def test_step_loss_exchange_two_ranks():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_step, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, transport, out in res:
+        assert transport == "allreduce"
+        for step, (mean, n, scale) in enumerate(out):
+            assert n == 7.0
+            assert mean == pytest.approx((20.0 * (step + 1) + 1.0) / 7.0)
+            # loss /= weight; loss *= world_size  ==  local mean * (n_local * world / n_global)
+            assert scale == pytest.approx((3 + rank) * 2 / 7.0)
+
+
+def test_step_loss_exchange_single_process():
+    from espnet_b200.sharding import StepLossExchange
+
+    ex = StepLossExchange(torch.device("cpu"), n_utt=4)
+    assert ex.transport == "none"
+    assert float(ex.step(torch.tensor(8.0))) == 2.0 and float(ex.scale()) == 1.0
