@@ -1,0 +1,8 @@
+"""Developer run: the C3 prefix-scoring walk with scoring_ids = top-15 (target of ncu launch lists)."""
+import sys, torch
+sys.path.insert(0, ".")
+import bench
+import oracle.stage_ref as sr
+sr.activate = lambda: False          # our path only under the profiler
+out = bench.bench_prefix(torch.device("cuda", 0), 6459.3, steps=int(sys.argv[1]) if len(sys.argv) > 1 else 6, snum=int(sys.argv[2]) if len(sys.argv) > 2 else 15)
+print(out["value"], out["us_per_step"])
