@@ -29,9 +29,6 @@ constexpr int kStreamGather = 3;  // label slots per thread held in registers
 constexpr int kStreamMaxSlots = 32;
 constexpr int kStreamSmemBudget = 200 * 1024;
 
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
 __device__ __forceinline__ uint64_t l2_evict_first_policy() {
   uint64_t pol;
   asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));

@@ -39,6 +39,15 @@ static void launch_full(const ScoreParams& p, cudaStream_t st) {
   // four tokens per thread when the rows of x, xmax, scores and log_psi can be read / written 16 bytes at a time
   const bool vec4 = p.V % 4 == 0 && NH <= 16 && ((uintptr_t)p.x | (uintptr_t)p.xmax | (uintptr_t)p.scores | (uintptr_t)p.log_psi) % 16 == 0;
   if (vec4) {
+    // bulk-copy ring (row B of the grid: the repeated-last-label entries)
+    const size_t smem = score_ring_smem<NH>();
+    if (set_max_smem_cached((const void*)prefix_score_ring_kernel<NH>, (int)smem) == cudaSuccess) {
+      dim3 grid((unsigned)((p.V + kRingTile - 1) / kRingTile), (unsigned)p.B + 1);
+      prefix_score_ring_kernel<NH><<<grid, kRingConsumers + 32, smem, st>>>(p);
+      return;
+    }
+  }
+  if (vec4) {
     // row B of the grid: the repeated-last-label entries
     dim3 grid((unsigned)((p.V / 4 + kScore4Threads - 1) / kScore4Threads), (unsigned)p.B + 1);
     prefix_score_full4_kernel<NH><<<grid, kScore4Threads, 0, st>>>(p);
@@ -90,7 +99,7 @@ extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const in
     prefix_fill_kernel<<<grid, 256, 0, st>>>(p);
     B200_CUDA(cudaGetLastError());
     const int n = p.n_bh * p.snum;
-    prefix_score_partial_kernel<<<(n + 127) / 128, 128, 0, st>>>(p);
+    prefix_score_partial_kernel<<<(n + 7) / 8, 256, 0, st>>>(p);  // a warp per (hypothesis, candidate)
   }
   B200_CUDA(cudaGetLastError());
   // pairs whose scaled sum underflowed: exact log-space redo (an empty queue costs one launch)

@@ -293,6 +293,178 @@ __global__ void __launch_bounds__(kScore4Threads) prefix_score_full4_kernel(Scor
   }
 }
 
+// The same computation with the log-probs arriving through a shared-memory RING of bulk (TMA) copies, as in the loss
+// stream kernel: a CTA owns a tile of kRingTile consecutive tokens of one utterance (1 KB per frame); one producer
+// warp issues one 1-D bulk copy per frame into the next free slot (kRingFrames frames per slot, completion counted
+// on the slot's `full` mbarrier, slots handed back through `empty`), the consumer warps (thread = four tokens)
+// take the slots in order.  Bytes in flight per SM are set by the ring, not by what a thread can keep in flight with
+// cp.async (prefix_score_full4_kernel).  Measured at C3: 107 us against 114 us -- with 512-token tiles (330 CTAs, three
+// per SM: two or three tiles per SM) it was SLOWER than cp.async (134 us); 256-token tiles give 660 CTAs, 4-5 per SM.
+// The kernel is issue-bound (about 60 issue slots per thread and frame for 16 bytes of x), not HBM-bound.
+constexpr int kRingTile = 256;     // tokens per CTA
+constexpr int kRingFrames = 4;     // frames per slot
+constexpr int kRingSlots = 6;
+constexpr int kRingConsumers = 64;
+constexpr int kRingRowBytes = kRingTile * 4;
+
+template <int NH>
+static size_t score_ring_smem() {
+  return 256 + sizeof(float) * kScoreTB * NH + (size_t)kRingSlots * kRingFrames * kRingRowBytes;
+}
+
+// (Packed fp32x2 FMAs -- fma.rn.f32x2, SASS FFMA2 -- were tried for the 4 x NH accumulators: 232 vs 164 us per C3 step;
+// 120 registers instead of 96 and the pack / unpack moves cost more than the halved FMA count saves.)
+template <int NH>
+__global__ void __launch_bounds__(kRingConsumers + 32) prefix_score_ring_kernel(ScoreParams p) {
+  extern __shared__ __align__(128) unsigned char rg_smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(rg_smem);            // [kRingSlots]
+  uint64_t* empty = full + kRingSlots;                               // [kRingSlots]
+  float* sE = reinterpret_cast<float*>(rg_smem + 256);               // [kScoreTB][NH]
+  unsigned char* ring = rg_smem + 256 + sizeof(float) * kScoreTB * NH;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (blockIdx.y == (unsigned)p.B) {
+    // one more row of CTAs: the repeated-last-label entries, a warp per hypothesis (the token CTAs skip them)
+    if (p.hyp_off != 0 || warp >= kRingConsumers / 32) return;
+    const int nwp = gridDim.x * (kRingConsumers / 32);
+    for (int h = blockIdx.x * (kRingConsumers / 32) + warp; h < p.n_bh; h += nwp) prefix_score_last_warp(p, h, lane);
+    return;
+  }
+  const int u = blockIdx.y;
+  const int tile0 = blockIdx.x * kRingTile;
+  const int ntok = min(kRingTile, p.V - tile0);       // V % 4 == 0
+  const uint32_t row_bytes = (uint32_t)ntok * 4u;
+  const int nfr = max(p.end - p.start, 0);
+  const int nstage = (nfr + kRingFrames - 1) / kRingFrames;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kRingSlots; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kRingConsumers / 32); }
+    mbar_fence_init();
+    fence_proxy_async();
+  }
+  __syncthreads();
+
+  if (warp == kRingConsumers / 32) {
+    // ------------------------------------------------------------------ producer
+    if (lane == 0) {
+      const float* xu = p.x + ((int64_t)u * p.T + p.start) * p.V + tile0;
+      int slot = 0;
+      uint32_t par = 0;  // parity of the `empty` completion that frees `slot` for its next use
+      for (int s = 0; s < nstage; ++s) {
+        if (s >= kRingSlots) mbar_wait(&empty[slot], par);
+        const int n = min(kRingFrames, nfr - s * kRingFrames);
+        mbar_arrive_expect_tx(&full[slot], (uint32_t)n * row_bytes);
+        for (int k = 0; k < n; ++k)
+          bulk_g2s(ring + ((size_t)slot * kRingFrames + k) * kRingRowBytes, xu + (int64_t)(s * kRingFrames + k) * p.V, row_bytes,
+                   &full[slot]);
+        if (++slot == kRingSlots) { slot = 0; if (s >= kRingSlots) par ^= 1u; }
+      }
+    }
+    return;
+  }
+
+  // -------------------------------------------------------------------- consumers
+  const int tid = threadIdx.x;  // 0 .. 127
+  const int c0 = tile0 + 4 * tid;
+  const bool live = 4 * tid < ntok;
+  const int cc = live ? c0 : tile0;
+  const int NHP = p.w.NHP;
+  const float4 mx4 = *reinterpret_cast<const float4*>(p.xmax + (int64_t)u * p.V + cc);
+  const float mx[4] = {mx4.x, mx4.y, mx4.z, mx4.w};
+  float mxl[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) mxl[q] = mx[q] * B200_LOG2E;
+  float acc[4][NH];
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int j = 0; j < NH; ++j) acc[q][j] = 0.f;
+  const uint32_t my_off = live ? 16u * (uint32_t)tid : 0u;
+
+  int slot = 0, st = 0;
+  uint32_t par = 0;
+  static_assert(kScoreTB % kRingFrames == 0, "slots do not straddle the blocks of E");
+  for (int tb = p.start; tb < p.end; tb += kScoreTB) {
+    const int nt = min(kScoreTB, p.end - tb);
+    asm volatile("bar.sync 1, %0;" ::"n"(kRingConsumers) : "memory");
+    // E rows for frames tb-1 .. tb+nt-2 (term t uses phi[t-1])
+    for (int i = tid; i < nt * NH; i += kRingConsumers) {
+      const int f = i / NH, j = i - f * NH + p.hyp_off;
+      sE[i] = j < NHP ? p.w.EA[((int64_t)u * p.T + (tb - 1 + f)) * NHP + j] : 0.f;
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(kRingConsumers) : "memory");
+    for (int f0 = 0; f0 < nt; f0 += kRingFrames, ++st) {
+      mbar_wait(&full[slot], par);
+      const unsigned char* base = ring + (size_t)slot * kRingFrames * kRingRowBytes + my_off;
+#pragma unroll
+      for (int k = 0; k < kRingFrames; ++k) {
+        const int f = f0 + k;
+        if (f < nt) {
+          const uint4 xv = *reinterpret_cast<const uint4*>(base + (size_t)k * kRingRowBytes);
+          float xh[4];
+          xh[0] = ex2f(fmaf(__uint_as_float(xv.x), B200_LOG2E, -mxl[0]));
+          xh[1] = ex2f(fmaf(__uint_as_float(xv.y), B200_LOG2E, -mxl[1]));
+          xh[2] = ex2f(fmaf(__uint_as_float(xv.z), B200_LOG2E, -mxl[2]));
+          xh[3] = ex2f(fmaf(__uint_as_float(xv.w), B200_LOG2E, -mxl[3]));
+          const float4* e4 = reinterpret_cast<const float4*>(sE + f * NH);
+#pragma unroll
+          for (int j4 = 0; j4 < NH / 4; ++j4) {
+            const float4 e = e4[j4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              acc[q][4 * j4 + 0] = fmaf(e.x, xh[q], acc[q][4 * j4 + 0]);
+              acc[q][4 * j4 + 1] = fmaf(e.y, xh[q], acc[q][4 * j4 + 1]);
+              acc[q][4 * j4 + 2] = fmaf(e.z, xh[q], acc[q][4 * j4 + 2]);
+              acc[q][4 * j4 + 3] = fmaf(e.w, xh[q], acc[q][4 * j4 + 3]);
+            }
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
+      if (++slot == kRingSlots) { slot = 0; par ^= 1u; }
+    }
+  }
+  if (!live) return;
+  float x0[4] = {B200_LZ, B200_LZ, B200_LZ, B200_LZ};  // r[0,n] = x[0,c]
+  if (p.output_len == 0) {
+    const float4 v = *reinterpret_cast<const float4*>(p.x + (int64_t)u * p.T * p.V + c0);
+    x0[0] = v.x; x0[1] = v.y; x0[2] = v.z; x0[3] = v.w;
+  }
+#pragma unroll
+  for (int j = 0; j < NH; ++j) {
+    if (j + p.hyp_off < p.n_hyps) {
+      const int h = u * p.n_hyps + j + p.hyp_off;
+      const float sp = p.s_prev ? p.s_prev[h] : 0.f;
+      const int64_t last = p.last_ids[h];
+      float psi[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int c = c0 + q;
+        if (c == p.blank) {
+          psi[q] = B200_LZ;
+        } else if (c == p.eos) {
+          psi[q] = p.w.REND[h];
+        } else {
+          psi[q] = finish_psi(acc[q][j], p.w.MA[h] + mx[q], x0[q]);
+          if ((int64_t)c != last) score_flag(p, acc[q][j], h, c);
+        }
+      }
+      if (last >= c0 && last < c0 + 4 && last != p.blank && last != p.eos) {
+        // the repeated-last-label entry belongs to the extra row of CTAs
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (c0 + q != (int)last) {
+            p.log_psi[(int64_t)h * p.V + c0 + q] = psi[q];
+            p.scores[(int64_t)h * p.V + c0 + q] = psi[q] - sp;
+          }
+      } else {
+        *reinterpret_cast<float4*>(p.log_psi + (int64_t)h * p.V + c0) = make_float4(psi[0], psi[1], psi[2], psi[3]);
+        *reinterpret_cast<float4*>(p.scores + (int64_t)h * p.V + c0) =
+            make_float4(psi[0] - sp, psi[1] - sp, psi[2] - sp, psi[3] - sp);
+      }
+    }
+  }
+}
+
 // Pre-beam subset (scoring_ids): rows are first filled with logzero, then one thread per
 // (hypothesis, candidate) pair.
 __global__ void prefix_fill_kernel(ScoreParams p) {
@@ -308,38 +480,43 @@ __global__ void prefix_fill_kernel(ScoreParams p) {
   (void)u;
 }
 
-__global__ void prefix_score_partial_kernel(ScoreParams p) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+// One WARP per (hypothesis, candidate) pair: the lanes split the frames (each x load is its own 32-byte sector, V
+// floats apart, so the loads of a warp are 32 independent sectors in flight) and the partial sums meet in one
+// shuffle reduction.  (One THREAD per pair walking all frames -- 500 dependent strided loads, 8 in flight -- took
+// 71 us at C3 with 15 candidates per hypothesis; this is the path BatchBeamSearch takes, batch_beam_search.py:228-238.)
+__global__ void __launch_bounds__(256) prefix_score_partial_kernel(ScoreParams p) {
+  const int lane = threadIdx.x & 31;
+  const int idx = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (idx >= p.n_bh * p.snum) return;
   const int h = idx / p.snum;
   const int u = h / p.n_hyps, j = h - u * p.n_hyps;
-  const int c = (int)p.scoring_ids[idx];
-  if (c < 0 || c >= p.V || c == p.blank || c == p.eos) return;  // filled already
+  const int64_t c64 = p.scoring_ids[idx];
+  if (c64 < 0 || c64 >= p.V || c64 == p.blank || c64 == p.eos) return;  // filled already
+  const int c = (int)c64;
   const int NHP = p.w.NHP;
-  const bool is_last = ((int64_t)c == p.last_ids[h]);
+  const bool is_last = (c64 == p.last_ids[h]);
   const float* E = (is_last ? p.w.EB : p.w.EA) + (int64_t)u * p.T * NHP + j;
   const float* xu = p.x + (int64_t)u * p.T * p.V + c;
   const float mx = p.xmax[(int64_t)u * p.V + c];
   const float mxl = mx * B200_LOG2E;
-  float a = 0.f;
-  for (int t0 = p.start; t0 < p.end; t0 += kScoreUnroll) {
-    float xv[kScoreUnroll], ev[kScoreUnroll];
-#pragma unroll
-    for (int k = 0; k < kScoreUnroll; ++k) {
-      const int t = t0 + k;
-      const bool ok = t < p.end;
-      xv[k] = ok ? ld_nc_f32(xu + (int64_t)t * p.V) : B200_LZ;
-      ev[k] = ok ? E[(int64_t)(t - 1) * NHP] : 0.f;
-    }
-#pragma unroll
-    for (int k = 0; k < kScoreUnroll; ++k) a = fmaf(ev[k], ex2f(fmaf(xv[k], B200_LOG2E, -mxl)), a);
+  float a0 = 0.f, a1 = 0.f;
+  int t = p.start + lane;
+  for (; t + 32 < p.end; t += 64) {  // two independent loads per lane and trip
+    const float x0 = ld_nc_f32(xu + (int64_t)t * p.V), x1 = ld_nc_f32(xu + (int64_t)(t + 32) * p.V);
+    const float e0 = E[(int64_t)(t - 1) * NHP], e1 = E[(int64_t)(t + 31) * NHP];
+    a0 = fmaf(e0, ex2f(fmaf(x0, B200_LOG2E, -mxl)), a0);
+    a1 = fmaf(e1, ex2f(fmaf(x1, B200_LOG2E, -mxl)), a1);
   }
-  const float x0 = (p.output_len == 0) ? xu[0] : B200_LZ;
-  const float psi = finish_psi(a, (is_last ? p.w.MB[h] : p.w.MA[h]) + mx, x0);
-  score_flag(p, a, h, c);
-  const float sp = p.s_prev ? p.s_prev[h] : 0.f;
-  p.log_psi[(int64_t)h * p.V + c] = psi;
-  p.scores[(int64_t)h * p.V + c] = psi - sp;
+  if (t < p.end) a0 = fmaf(E[(int64_t)(t - 1) * NHP], ex2f(fmaf(ld_nc_f32(xu + (int64_t)t * p.V), B200_LOG2E, -mxl)), a0);
+  const float a = warp_sum(a0 + a1);
+  if (lane == 0) {
+    const float x0 = (p.output_len == 0) ? xu[0] : B200_LZ;
+    const float psi = finish_psi(a, (is_last ? p.w.MB[h] : p.w.MA[h]) + mx, x0);
+    score_flag(p, a, h, c);
+    const float sp = p.s_prev ? p.s_prev[h] : 0.f;
+    p.log_psi[(int64_t)h * p.V + c] = psi;
+    p.scores[(int64_t)h * p.V + c] = psi - sp;
+  }
 }
 
 // Exact log-space redo of the queued (hypothesis, token) pairs (ctc_prefix_score.py:165-180 as written:

@@ -121,12 +121,12 @@ class CTCPrefixScoreB200(object):
             else:
                 s_prev = None if s_prev == 0.0 else torch.full((n_bh,), float(s_prev), device=self.device)
 
+        # (the reference also builds scoring_idmap (n_bh, O) here, the inverse of scoring_ids, to find a candidate's
+        # slice of its r tensor later (ctc_prefix_score.py:100-115,208-214); r is recomputed per survivor here, so the
+        # map -- a 12.8 MB fill + scatter per step at C3 -- has no reader: the state keeps None in its place)
         scoring_idmap = None
         if self.scoring_num > 0:
             scoring_ids = scoring_ids.to(device=self.device, dtype=torch.int64).contiguous()
-            scoring_idmap = torch.full((n_bh, O), -1, dtype=torch.long, device=self.device)
-            scoring_idmap.scatter_(1, scoring_ids, torch.arange(self.scoring_num, device=self.device)
-                                   .expand(n_bh, -1))
 
         # frame window from the attention weights (ctc_prefix_score.py:145-154)
         if att_w is not None and self.margin > 0:
