@@ -36,6 +36,7 @@ SIGNATURES = {
                                       _i64, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "b200_ctc_debug_force_log_sweep": (_int, [_int]),
     "b200_ctc_stage_labels": (_int, [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _vp, _vp]),
+    "b200_ctc_stage_labels_pinned": (_int, [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _vp]),
     "b200_ctc_loss_status": (_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
     "b200_ctc_grad_rescale": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _i64, _f32, _vp, _vp]),
     "b200_ctc_greedy": (_int, [_vp, _int, _i64, _i64, _i64, _i64, _i64, _vp, _vp]),

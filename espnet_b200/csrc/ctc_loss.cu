@@ -2,6 +2,8 @@
 // See ctc_loss.cuh for the kernel map and include/espnet_b200_ctc.h for the ABI.
 #include "ctc_loss.cuh"
 
+#include <mutex>
+
 namespace b200 {
 
 // ============================================================================

@@ -303,10 +303,10 @@ extern "C" int b200_ctc_debug_force_log_sweep(int on) {
   return was;
 }
 
-extern "C" int b200_ctc_stage_labels(const int64_t* targets_host, int64_t n_targets, const int64_t* tgt_offsets_host,
-                                     const int64_t* ilen_host, const int64_t* olen_host, int64_t B,
-                                     int64_t* pinned_host, int64_t* dev, void* stream) {
-  B200_CHECK_ARG((targets_host || n_targets == 0) && ilen_host && olen_host && pinned_host && dev,
+// the label side of a call laid out in one host buffer: targets | offsets (B) | ilen (B) | olen (B)
+static int stage_labels_fill(const int64_t* targets_host, int64_t n_targets, const int64_t* tgt_offsets_host,
+                             const int64_t* ilen_host, const int64_t* olen_host, int64_t B, int64_t* pinned_host) {
+  B200_CHECK_ARG((targets_host || n_targets == 0) && ilen_host && olen_host && pinned_host,
                  B200_ERR_INVALID_ARGUMENT, "null pointer argument");
   B200_CHECK_ARG(n_targets >= 0 && B >= 1, B200_ERR_INVALID_ARGUMENT, "bad sizes");
   int64_t* q = pinned_host;
@@ -320,8 +320,84 @@ extern "C" int b200_ctc_stage_labels(const int64_t* targets_host, int64_t n_targ
   }
   memcpy(q + B, ilen_host, sizeof(int64_t) * (size_t)B);
   memcpy(q + 2 * B, olen_host, sizeof(int64_t) * (size_t)B);
+  return B200_OK;
+}
+
+extern "C" int b200_ctc_stage_labels(const int64_t* targets_host, int64_t n_targets, const int64_t* tgt_offsets_host,
+                                     const int64_t* ilen_host, const int64_t* olen_host, int64_t B,
+                                     int64_t* pinned_host, int64_t* dev, void* stream) {
+  B200_CHECK_ARG(dev != nullptr, B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  const int rc = stage_labels_fill(targets_host, n_targets, tgt_offsets_host, ilen_host, olen_host, B, pinned_host);
+  if (rc) return rc;
   B200_CUDA(cudaMemcpyAsync(dev, pinned_host, sizeof(int64_t) * (size_t)(n_targets + 3 * B), cudaMemcpyHostToDevice,
                             (cudaStream_t)stream));
+  return B200_OK;
+}
+
+// ---- the same with the pinned staging buffers owned by the library: a small ring per device, each slot guarded by
+// an event recorded after its copy (a slot is rewritten only when that copy has completed)
+namespace b200 {
+// The staged labels travel by a KERNEL that reads the page-locked host buffer over PCIe (cudaHostAlloc memory is
+// device-accessible under unified addressing) instead of a copy-engine transfer: between two kernels of one stream a
+// cudaMemcpyAsync costs ~14 us of engine hand-over (measured at C2, tools/dev_gap.py), this kernel ~3 us, and as a
+// programmatic dependent its launch hides under the tail of the grid before it.
+__global__ void __launch_bounds__(1024) ctc_label_fetch_kernel(const int4* __restrict__ src, int4* __restrict__ dst, int n16) {
+  pdl_launch_dependents();
+  pdl_wait();  // earlier grids of the stream may still read the destination (a recycled allocation)
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += gridDim.x * blockDim.x) {
+    int4 v;
+    asm volatile("ld.volatile.global.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(src + i) : "memory");
+    dst[i] = v;
+  }
+}
+}  // namespace b200
+
+namespace {
+struct PinSlot {
+  int64_t* buf = nullptr;
+  size_t cap = 0;
+  cudaEvent_t ev = nullptr;
+  bool busy = false;
+};
+struct PinRing {
+  PinSlot slot[16];
+  int next = 0;
+};
+PinRing g_pin[64];
+std::mutex g_pin_mu;
+}  // namespace
+
+extern "C" int b200_ctc_stage_labels_pinned(const int64_t* targets_host, int64_t n_targets, const int64_t* tgt_offsets_host,
+                                            const int64_t* ilen_host, const int64_t* olen_host, int64_t B, int64_t* dev,
+                                            void* stream) {
+  B200_CHECK_ARG(n_targets >= 0 && B >= 1, B200_ERR_INVALID_ARGUMENT, "bad sizes");
+  int d = 0;
+  B200_CUDA(cudaGetDevice(&d));
+  B200_CHECK_ARG(d >= 0 && d < 64, B200_ERR_INVALID_ARGUMENT, "device index %d outside [0,64)", d);
+  B200_CHECK_ARG(dev != nullptr && (reinterpret_cast<uintptr_t>(dev) & 15) == 0, B200_ERR_INVALID_ARGUMENT,
+                 "the device destination must be 16-byte aligned");
+  const size_t n = (size_t)(n_targets + 3 * B);
+  std::lock_guard<std::mutex> lk(g_pin_mu);
+  PinRing& ring = g_pin[d];
+  PinSlot& s = ring.slot[ring.next];
+  ring.next = (ring.next + 1) % 16;
+  if (s.busy) B200_CUDA(cudaEventSynchronize(s.ev));
+  if (s.cap < n) {
+    if (s.buf) B200_CUDA(cudaFreeHost(s.buf));
+    s.buf = nullptr;
+    s.cap = 0;
+    const size_t cap = n < 16384 ? 16384 : n + n / 2 + 2;
+    B200_CUDA(cudaHostAlloc((void**)&s.buf, cap * sizeof(int64_t), cudaHostAllocDefault));  // HOST memory
+    s.cap = cap;
+  }
+  if (!s.ev) B200_CUDA(cudaEventCreateWithFlags(&s.ev, cudaEventDisableTiming));
+  const int rc = stage_labels_fill(targets_host, n_targets, tgt_offsets_host, ilen_host, olen_host, B, s.buf);
+  if (rc) return rc;
+  const int n16 = (int)((n * sizeof(int64_t) + 15) / 16);  // (the pinned buffer holds >= n + 1 words; see the header for dev)
+  B200_CUDA(launch_kernel(ctc_label_fetch_kernel, dim3((unsigned)((n16 + 1023) / 1024 > 8 ? 8 : (n16 + 1023) / 1024)), dim3(1024), 0,
+                          (cudaStream_t)stream, true, reinterpret_cast<const int4*>(s.buf), reinterpret_cast<int4*>(dev), n16));
+  B200_CUDA(cudaEventRecord(s.ev, (cudaStream_t)stream));
+  s.busy = true;
   return B200_OK;
 }
 

@@ -150,6 +150,7 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
     mbar_fence_init();
   }
   __syncthreads();
+  pdl_wait();  // (launched as a programmatic dependent of whatever precedes it on the stream: labels, logits)
   // This kernel reads the caller's int64 labels itself (clamped exactly as the prep kernel clamps them), so
   // it does not wait for the prep kernel: prep is launched AFTER it as a programmatic dependent and runs
   // on the free thread slots of the SMs while the rows stream.
@@ -398,7 +399,7 @@ static int launch_stream_t(const LossParams& p, const StreamCfg& c, cudaStream_t
   auto go = [&](auto kern) -> int {
     B200_CUDA(set_max_smem_cached((const void*)kern, c.smem));
     B200_CUDA(launch_kernel(kern, dim3((unsigned)g), dim3((kStreamWarps + 1) * 32), (size_t)c.smem, st,
-                            false, p, c.nslots, c.slot_bytes));
+                            true, p, c.nslots, c.slot_bytes));
     return B200_OK;
   };
   if (c.group == 1) return go(ctc_stream_kernel<T, 1>);

@@ -157,6 +157,14 @@ __global__ void __launch_bounds__(256) ctc_grad_rescale_kernel(T* __restrict__ g
   V = V > 0 ? V : -V;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const float inv = 1.0f / expected;
+  pdl_launch_dependents();
+  pdl_wait();  // (a programmatic dependent of the grid before it: the upstream gradient, the patch kernel's stores)
+  {
+    // the usual case first: every ratio is exactly 1 and there is nothing to do
+    bool same = true;
+    for (int b = lane; b < (gout_n == 1 ? 1 : (int)B); b += 32) same = same && (gout[b] * inv == 1.0f);
+    if (__all_sync(0xffffffffu, same)) return;
+  }
   for (int64_t r = (int64_t)blockIdx.x * nwarp + warp; r < B * Tn; r += (int64_t)gridDim.x * nwarp) {
     const int64_t b = r / Tn, t = r - b * Tn;
     const float ratio = gout[gout_n == 1 ? 0 : b] * inv;
@@ -184,9 +192,8 @@ static int launch_rescale(void* grad, int64_t Tn, int64_t B, int64_t V, int64_t 
   const int64_t cap = (int64_t)num_sms() * 8;
   if (g > cap) g = cap;
   // (unaligned rows: V is passed as 0 vectors by giving the scalar loop the whole row)
-  ctc_grad_rescale_kernel<T><<<(unsigned)g, 256, 0, st>>>((T*)grad, Tn, B, vec ? (int)V : -(int)V, gstride_t, gstride_b,
-                                                         gout, gout_n, expected, ilen);
-  B200_CUDA(cudaGetLastError());
+  B200_CUDA(launch_kernel(ctc_grad_rescale_kernel<T>, dim3((unsigned)g), dim3(256), 0, st, true, (T*)grad, Tn, B,
+                          vec ? (int)V : -(int)V, gstride_t, gstride_b, gout, gout_n, expected, ilen));
   return B200_OK;
 }
 

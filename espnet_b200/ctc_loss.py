@@ -94,6 +94,10 @@ def _h64(x):
     return x if x.is_contiguous() else x.contiguous()
 
 
+def _is_host(x):
+    return not (torch.is_tensor(x) and x.is_cuda)
+
+
 def _host_np(x):
     """int64 numpy view / copy of a host-side length or label vector (tensor, list, numpy)."""
     if torch.is_tensor(x):
@@ -157,46 +161,49 @@ class _Plan(object):
         dev = logits.device
         self.logits = logits
         self.T, self.B, self.V = T, B, V = logits.shape
-        self.lmax = int(lmax)
+        self.lmax = lmax = int(lmax)
         self.blank = int(blank)
         self.dtype = _lib.dtype_code(logits.dtype)
-        self.stream = torch._C._cuda_getCurrentRawStream(dev.index) if dev.type == "cuda" else 0
+        self.stream = stream = torch._C._cuda_getCurrentRawStream(dev.index) if dev.type == "cuda" else 0
         lib = _lib.load()
-        host = [not (torch.is_tensor(p) and p.is_cuda) for p in (targets, ilen, olen)]
-        if all(host) and not (torch.is_tensor(tgt_offsets) and tgt_offsets.is_cuda) and dev.type == "cuda":
-            # the usual trainer-side call: labels and lengths arrive from the data loader on the host.  ONE pinned
-            # staging buffer, ONE asynchronous copy (laid out by the library), four pointers into the device copy
-            tg, il, ol = _h64(targets).reshape(-1), _h64(ilen).reshape(-1), _h64(olen).reshape(-1)
-            off = None if tgt_offsets is None else _h64(tgt_offsets).reshape(-1)
+        key = (T, B, V, lmax)
+        nbytes = _ws_bytes_cache.get(key)
+        if nbytes is None:
+            nbytes = _ws_bytes_cache[key] = lib.b200_ctc_loss_workspace_bytes(*key)
+        self.ws_bytes = nbytes
+        if (dev.type == "cuda" and _is_host(targets) and _is_host(ilen) and _is_host(olen)
+                and (tgt_offsets is None or _is_host(tgt_offsets))):
+            # the usual trainer-side call: labels and lengths arrive from the data loader on the host.  The library
+            # lays them out in one of its pinned staging buffers and issues ONE asynchronous copy; the device copy,
+            # the nll vector and the workspace share ONE allocation
+            tg, il, ol = _h64(targets), _h64(ilen), _h64(olen)
+            off = None if tgt_offsets is None else _h64(tgt_offsets)
             if il.numel() != B or ol.numel() != B or (off is not None and off.numel() != B):
                 raise RuntimeError("ilen, olen and tgt_offsets must have one entry per utterance")
             nt = tg.numel()
-            n = nt + 3 * B
-            ring = _ring(dev)
-            slot = ring.take(n)
-            buf = torch.empty(n, dtype=torch.int64, device=dev)
-            base = buf.data_ptr()
+            lab = (8 * (nt + 3 * B) + 255) & ~255
+            nlb = (4 * B + 255) & ~255
+            self.keep = pool = torch.empty(lab + nlb + nbytes + 256, dtype=torch.uint8, device=dev)
+            base = (pool.data_ptr() + 255) & ~255
             with _on(dev):
-                rc = lib.b200_ctc_stage_labels(tg.data_ptr(), nt, None if off is None else off.data_ptr(), il.data_ptr(),
-                                               ol.data_ptr(), B, ring.ptr[slot], base, self.stream)
-            _lib.check(rc, "b200_ctc_stage_labels")
-            ring.sent(slot, torch.cuda.current_stream(dev))
-            self.keep = buf
+                rc = lib.b200_ctc_stage_labels_pinned(tg.data_ptr(), nt, None if off is None else off.data_ptr(),
+                                                      il.data_ptr(), ol.data_ptr(), B, base, stream)
+            if rc:
+                _lib.check(rc, "b200_ctc_stage_labels_pinned")
             self.targets_ptr, self.offsets_ptr = base, base + 8 * nt
             self.ilen_ptr, self.olen_ptr = base + 8 * (nt + B), base + 8 * (nt + 2 * B)
+            self.nll_ptr = base + lab
+            self.ws_ptr = base + lab + nlb
         else:
             t = pack_labels(targets, tgt_offsets, ilen, olen, dev)
             if t[2].numel() != B or t[3].numel() != B or t[1].numel() != B:
                 raise RuntimeError("ilen, olen and tgt_offsets must have one entry per utterance")
-            self.keep = t
             self.targets_ptr, self.offsets_ptr, self.ilen_ptr, self.olen_ptr = (x.data_ptr() for x in t)
-        key = (T, B, V, self.lmax)
-        nbytes = _ws_bytes_cache.get(key)
-        if nbytes is None:
-            nbytes = _ws_bytes_cache[key] = lib.b200_ctc_loss_workspace_bytes(*key)
-        self.workspace = torch.empty(nbytes + 256, dtype=torch.uint8, device=dev)
-        self.ws_ptr = (self.workspace.data_ptr() + 255) // 256 * 256
-        self.ws_bytes = nbytes
+            nlb = (4 * B + 255) & ~255
+            workspace = torch.empty(nlb + nbytes + 256, dtype=torch.uint8, device=dev)
+            self.keep = (t, workspace)
+            self.nll_ptr = (workspace.data_ptr() + 255) // 256 * 256
+            self.ws_ptr = self.nll_ptr + nlb
 
     def common_args(self):
         x = self.logits
@@ -265,17 +272,20 @@ class _CTCLossFunction(torch.autograd.Function):
         logits = _prep_logits(logits)
         plan = _Plan(logits, targets, tgt_offsets, ilen, olen, lmax, blank)
         dev = logits.device
-        nll = torch.empty(plan.B, dtype=torch.float32, device=dev)
         reduced = reduce_scale is not None
-        loss = torch.empty((), dtype=torch.float32, device=dev) if reduced else None
-        loss_ptr, s = (loss.data_ptr(), float(reduce_scale)) if reduced else (None, 1.0)
+        if reduced:   # the per-utterance nll is not returned: it lives in the plan's allocation
+            loss = torch.empty((), dtype=torch.float32, device=dev)
+            nll_ptr, loss_ptr, s = plan.nll_ptr, loss.data_ptr(), float(reduce_scale)
+        else:
+            nll = torch.empty(plan.B, dtype=torch.float32, device=dev)
+            nll_ptr, loss_ptr, s = nll.data_ptr(), None, 1.0
         ctx.hint = float(hint)
         lib = _lib.load()
         if ctx.needs_input_grad[0]:
             grad = _empty_like_strided(logits)
             with _on(dev):
                 rc = lib.b200_ctc_loss_fwd_bwd(
-                    *plan.common_args(), None, ctx.hint * s, nll.data_ptr(), loss_ptr, s, grad.data_ptr(),
+                    *plan.common_args(), None, ctx.hint * s, nll_ptr, loss_ptr, s, grad.data_ptr(),
                     grad.stride(0), grad.stride(1), plan.ws_ptr, plan.ws_bytes, plan.stream)
             if rc:
                 _lib.check(rc, "b200_ctc_loss_fwd_bwd")
@@ -284,7 +294,7 @@ class _CTCLossFunction(torch.autograd.Function):
         else:
             with _on(dev):
                 rc = lib.b200_ctc_loss_forward(
-                    *plan.common_args(), nll.data_ptr(), loss_ptr, s, plan.ws_ptr, plan.ws_bytes, plan.stream)
+                    *plan.common_args(), nll_ptr, loss_ptr, s, plan.ws_ptr, plan.ws_bytes, plan.stream)
             _lib.check(rc, "b200_ctc_loss_forward")
         if strict:
             _check_strict(plan)

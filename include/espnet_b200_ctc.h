@@ -164,6 +164,17 @@ int b200_ctc_stage_labels(const int64_t* targets_host, int64_t n_targets,
                           const int64_t* ilen_host, const int64_t* olen_host, int64_t B,
                           int64_t* pinned_host, int64_t* dev, void* stream);
 
+/* The same with the pinned staging buffers owned by the library (a ring of 16 per device, grown on demand
+ * with cudaHostAlloc -- page-locked HOST memory, never device memory -- each slot guarded by an event
+ * recorded after its transfer).  The caller passes pageable host arrays and the device destination only.
+ * The words travel by a small kernel on `stream` that reads the page-locked buffer over PCIe (no copy-engine
+ * hand-over between the kernels of a step).  dev: 16-byte aligned, room for n_targets + 3*B words rounded
+ * up to an even count. */
+int b200_ctc_stage_labels_pinned(const int64_t* targets_host, int64_t n_targets,
+                                 const int64_t* tgt_offsets_host,
+                                 const int64_t* ilen_host, const int64_t* olen_host, int64_t B,
+                                 int64_t* dev, void* stream);
+
 /* Selects the lattice sweeps of _fwd_bwd.  on != 0 (the default): log-domain sweeps.  on == 0: float64
  * linear-domain sweeps (Lmax <= 255), whose patch kernel certifies every row it decodes and hands the
  * utterances it cannot certify (dynamic range) to the log-domain kernels; same results within the parity
