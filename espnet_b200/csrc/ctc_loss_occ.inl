@@ -30,9 +30,9 @@ constexpr int kOccMaxStages = 4;  // rows in flight per warp
 // floats of one stage (alpha row, beta row, lpg row) and of one warp's share of shared memory:
 // stages, un-normalised occupancies [2][Kp], label columns [Kp], 16-bit duplicate codes [Kp]
 // (+16: the block scale exponents of the alpha and of the beta sweep for the row's chunks, linear lattice only)
-__host__ __device__ inline int64_t occ_stage_floats(int64_t Kp) { return 5 * Kp + 16; }
-__host__ __device__ inline int64_t occ_warp_floats(int64_t Kp, int stages) {
-  return stages * occ_stage_floats(Kp) + 3 * Kp + Kp / 2;
+__host__ __device__ inline int64_t occ_stage_floats(int64_t Kp, bool lin) { return 5 * Kp + (lin ? 16 : 0); }
+__host__ __device__ inline int64_t occ_warp_floats(int64_t Kp, int stages, bool lin) {
+  return stages * occ_stage_floats(Kp, lin) + 3 * Kp + Kp / 2;
 }
 // 16-bit form of LossWs::dupcode (next position + 1 <= 1023)
 constexpr int kDup16Later = 0x8000;
@@ -50,12 +50,12 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int64_t Kp = p.ws.Kp, Sp = p.ws.Sp;
   const int T_ = (int)p.T;
-  const int64_t stagef = occ_stage_floats(Kp);
-  float* wbase = reinterpret_cast<float*>(occ_smem) + warp * occ_warp_floats(Kp, stages);
+  const int64_t stagef = occ_stage_floats(Kp, LIN);
+  float* wbase = reinterpret_cast<float*>(occ_smem) + warp * occ_warp_floats(Kp, stages, LIN);
   float* scratch = wbase + stages * stagef;               // [2][Kp] un-normalised occupancies of the label states
   int* s_lab = reinterpret_cast<int*>(scratch + 2 * Kp);  // [Kp] label columns of the unit's utterance
   unsigned short* s_dup = reinterpret_cast<unsigned short*>(s_lab + Kp);  // [Kp] its duplicate codes
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<float*>(occ_smem) + nwarps * occ_warp_floats(Kp, stages)) +
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<float*>(occ_smem) + nwarps * occ_warp_floats(Kp, stages, LIN)) +
                    warp * kOccMaxStages;
   if (lane == 0) {
     for (int s = 0; s < stages; ++s) mbar_init(&bars[s], 1);
@@ -408,12 +408,12 @@ struct OccPlan {
 
 // Largest pipeline that fits: 8 warps x up to 4 stages with two CTAs per SM if the rows are short,
 // fewer warps / stages and one CTA per SM for long label sequences (a row is 20 * Kp bytes).
-static OccPlan plan_occ(int64_t Kp) {
+static OccPlan plan_occ(int64_t Kp, bool lin) {
   const size_t budgets[2] = {112u * 1024u, (size_t)max_smem_optin() - 1024u};
   for (size_t budget : budgets) {
     for (int warps = 8; warps >= 1; warps >>= 1) {
       for (int stages = kOccMaxStages; stages >= 2; --stages) {
-        const size_t smem = (size_t)warps * ((size_t)occ_warp_floats(Kp, stages) * 4 + kOccMaxStages * 8);
+        const size_t smem = (size_t)warps * ((size_t)occ_warp_floats(Kp, stages, lin) * 4 + kOccMaxStages * 8);
         if (smem <= budget) return OccPlan{warps, stages, smem};
       }
     }
@@ -423,7 +423,7 @@ static OccPlan plan_occ(int64_t Kp) {
 
 template <typename T, bool PATCH, int NJ, bool LIN>
 static int launch_occ_nj(const LossParams& p, cudaStream_t st) {
-  const OccPlan pl = plan_occ(p.ws.Kp);
+  const OccPlan pl = plan_occ(p.ws.Kp, LIN);
   B200_CHECK_ARG(pl.warps > 0, B200_ERR_UNSUPPORTED_SHAPE, "Lmax=%lld: a lattice row does not fit in shared memory",
                  (long long)p.Lmax);
   B200_CUDA(set_max_smem_cached((const void*)ctc_occ_kernel<T, PATCH, NJ, LIN>, (int)pl.smem));

@@ -127,4 +127,5 @@ __global__ void prefix_phi_kernel(const float* __restrict__ r_prev, const int64_
 }  // namespace b200
 
 #include "ctc_prefix_score.inl"
+#include "ctc_prefix_mma.inl"
 #include "ctc_prefix_host.inl"

@@ -1,6 +1,10 @@
 // ctc_prefix_host.inl -- extern "C" entry points of CTC prefix scoring.
 using namespace b200;
 
+// developer switch: the fp32 score kernels instead of the tensor-core one (A/B timing, parity of the fallback)
+static int g_prefix_no_mma = 0;
+extern "C" void b200_ctc_debug_prefix_fp32_score(int on) { g_prefix_no_mma = on; }
+
 extern "C" int b200_ctc_prefix_init(float* x, const int64_t* xlens, int64_t B, int64_t T, int64_t V, int blank,
                                     float* r0, float* xmax, void* stream) {
   B200_CHECK_ARG(x && xlens && r0 && xmax, B200_ERR_INVALID_ARGUMENT, "null pointer argument");
@@ -32,6 +36,24 @@ static int check_prefix(int64_t B, int64_t T, int64_t V, int64_t n_hyps, int bla
                  "frame window [%lld,%lld) must satisfy 1 <= start, end <= T=%lld", (long long)start,
                  (long long)end, (long long)T);
   return B200_OK;
+}
+
+// all candidates on the tensor cores (ctc_prefix_mma.inl): up to 16 hypotheses of every utterance per launch
+static bool launch_full_mma(const ScoreParams& p, cudaStream_t st) {
+  const bool vec4 = p.V % 4 == 0 && ((uintptr_t)p.x | (uintptr_t)p.xmax | (uintptr_t)p.scores | (uintptr_t)p.log_psi) % 16 == 0;
+  if (!vec4 || g_prefix_no_mma == 1) return false;
+  const size_t smem = score_mma_smem();
+  dim3 grid((unsigned)((p.V + kMmaTile - 1) / kMmaTile), (unsigned)p.B + 1);  // row B: the repeated-last-label entries
+#ifdef B200_PREFIX_DBG
+  if (g_prefix_no_mma == 2) {  // developer build: the copies alone
+    if (set_max_smem_cached((const void*)prefix_score_mma_kernel<1>, (int)smem) != cudaSuccess) return false;
+    prefix_score_mma_kernel<1><<<grid, kMmaConsumers + 32, smem, st>>>(p);
+    return true;
+  }
+#endif
+  if (set_max_smem_cached((const void*)prefix_score_mma_kernel<0>, (int)smem) != cudaSuccess) return false;
+  prefix_score_mma_kernel<0><<<grid, kMmaConsumers + 32, smem, st>>>(p);
+  return true;
 }
 
 template <int NH>
@@ -84,7 +106,11 @@ extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const in
   B200_CUDA(cudaGetLastError());
   p.hyp_off = 0;
   if (snum == 0) {
-    if (n_hyps <= 4) launch_full<4>(p, st);
+    bool mma = true;
+    for (; mma && p.hyp_off < (int)n_hyps; p.hyp_off += 16) mma = launch_full_mma(p, st);
+    p.hyp_off = 0;
+    if (mma) {
+    } else if (n_hyps <= 4) launch_full<4>(p, st);
     else if (n_hyps <= 8) launch_full<8>(p, st);
     else if (n_hyps <= 12) launch_full<12>(p, st);
     else if (n_hyps <= 16) launch_full<16>(p, st);

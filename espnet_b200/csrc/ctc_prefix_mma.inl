@@ -1,0 +1,231 @@
+// ctc_prefix_mma.inl -- the full-vocabulary score kernel of CTC prefix scoring on the tensor cores.
+//
+// For one utterance the scaled sums of ctc_prefix_score.py:144-148,
+//     acc[h][c] = sum_t E[t-1][h] * 2^(x[t][c] * log2e - max_t x[.][c] * log2e),
+// are a (hypotheses x frames) x (frames x tokens) product with at most 16 rows.  The fp32 kernels above spend one
+// FFMA per (hypothesis, frame, token) -- ~100 issue slots per thread and frame for 16 bytes of x, 57 % issue
+// utilisation at 3 TB/s (ncu, r02) -- so the product goes to mma.sync m16n8k8 here: rows = hypotheses, k = 8
+// frames, n = 8 tokens, ~6.5 issue slots per element of x.  TF32 operands carry 11 significant bits, not enough
+// for the 1e-4 bar on log_psi, so both operands are split into a TF32 head and a TF32 tail and three products are
+// accumulated in fp32 (head*head + tail*head + head*tail; what is dropped is below 2^-21 relative per term).
+//
+// The rows of x arrive as in prefix_score_ring_kernel: one producer lane, 1-D bulk copies of 256-token rows into a
+// ring of 8-frame slots (rows padded to 264 floats: the B fragments of a warp then read 32 distinct banks).
+namespace b200 {
+
+constexpr int kMmaTile = 256;          // tokens per CTA
+constexpr int kMmaWarpTok = 64;        // tokens per consumer warp (8 n-tiles)
+constexpr int kMmaNT = kMmaWarpTok / 8;
+constexpr int kMmaConsumers = (kMmaTile / kMmaWarpTok) * 32;
+constexpr int kMmaRow = kMmaTile + 8;  // floats between two rows of a slot
+constexpr int kMmaSlots = 4;
+constexpr int kMmaTB = 64;             // frames of E staged per block
+constexpr int kMmaES = 24;             // floats between two frames of the staged E (16 used)
+
+static size_t score_mma_smem() {
+  return 256 + sizeof(float) * kMmaTB * kMmaES + sizeof(float) * (size_t)kMmaSlots * 8 * kMmaRow;
+}
+
+__device__ __forceinline__ float mma_lds_f32(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// v = head + tail with head = the 19 leading bits of v (exactly a TF32 value); the tail is exact in fp32
+__device__ __forceinline__ void tf32_split(float v, uint32_t& head, uint32_t& tail) {
+  head = __float_as_uint(v) & 0xffffe000u;
+  tail = __float_as_uint(v - __uint_as_float(head));
+}
+
+template <int DBG>
+__global__ void __launch_bounds__(kMmaConsumers + 32, 5) prefix_score_mma_kernel(ScoreParams p) {
+  extern __shared__ __align__(128) unsigned char mm_smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(mm_smem);  // [kMmaSlots]
+  uint64_t* empty = full + kMmaSlots;                     // [kMmaSlots]
+  float* sE = reinterpret_cast<float*>(mm_smem + 256);    // [kMmaTB][kMmaES]
+  float* ring = sE + kMmaTB * kMmaES;                     // [kMmaSlots][8][kMmaRow]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NCW = kMmaConsumers / 32;
+  if (blockIdx.y == (unsigned)p.B) {
+    // one more row of CTAs: the repeated-last-label entries, a warp per hypothesis (the token CTAs skip them)
+    if (p.hyp_off != 0 || warp >= NCW) return;
+    const int nwp = gridDim.x * NCW;
+    for (int h = blockIdx.x * NCW + warp; h < p.n_bh; h += nwp) prefix_score_last_warp(p, h, lane);
+    return;
+  }
+  const int u = blockIdx.y;
+  const int tile0 = blockIdx.x * kMmaTile;
+  const int ntok = min(kMmaTile, p.V - tile0);  // V % 4 == 0
+  const uint32_t row_bytes = (uint32_t)ntok * 4u;
+  const int nfr = max(p.end - p.start, 0);
+  const int nstage = (nfr + 7) / 8;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kMmaSlots; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NCW); }
+    mbar_fence_init();
+    fence_proxy_async();
+  }
+  __syncthreads();
+
+  if (warp == NCW) {
+    // ------------------------------------------------------------------ producer
+    if (lane == 0) {
+      const float* xu = p.x + ((int64_t)u * p.T + p.start) * p.V + tile0;
+      int slot = 0;
+      uint32_t par = 0;  // parity of the `empty` completion that frees `slot` for its next use
+      for (int s = 0; s < nstage; ++s) {
+        if (s >= kMmaSlots) mbar_wait(&empty[slot], par);
+        const int n = min(8, nfr - s * 8);
+        mbar_arrive_expect_tx(&full[slot], (uint32_t)n * row_bytes);
+        for (int k = 0; k < n; ++k)
+          bulk_g2s(ring + ((size_t)slot * 8 + k) * kMmaRow, xu + (int64_t)(s * 8 + k) * p.V, row_bytes, &full[slot]);
+        if (++slot == kMmaSlots) { slot = 0; if (s >= kMmaSlots) par ^= 1u; }
+      }
+    }
+    return;
+  }
+
+  // -------------------------------------------------------------------- consumers
+  const int tid = threadIdx.x;          // 0 .. kMmaConsumers-1
+  const int gid = lane >> 2, tig = lane & 3;
+  const int wtok = warp * kMmaWarpTok;  // first token of this warp inside the tile
+  const int NHP = p.w.NHP;
+  // B fragments: token wtok + 8*nt + gid of frames tig and tig + 4 of the slot
+  float mxl[kMmaNT];
+#pragma unroll
+  for (int nt = 0; nt < kMmaNT; ++nt) {
+    const int c = tile0 + wtok + 8 * nt + gid;
+    mxl[nt] = (c < p.V ? p.xmax[(int64_t)u * p.V + c] : 0.f) * B200_LOG2E;
+  }
+  float acc[kMmaNT][4];
+#pragma unroll
+  for (int nt = 0; nt < kMmaNT; ++nt)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc[nt][q] = 0.f;
+  const uint32_t b_off = (uint32_t)((tig * kMmaRow + wtok + gid) * 4);
+  const uint32_t ring_u32 = smem_u32(ring);
+
+  int slot = 0;
+  uint32_t par = 0;
+  for (int tb = p.start; tb < p.end; tb += kMmaTB) {
+    const int nt_blk = min(kMmaTB, p.end - tb);
+    asm volatile("bar.sync 1, %0;" ::"n"(kMmaConsumers) : "memory");
+    // E rows for frames tb-1 .. tb+nt_blk-2 (term t uses phi[t-1]); zero beyond the block and beyond the hypotheses
+    for (int i = tid; i < kMmaTB * 16; i += kMmaConsumers) {
+      const int f = i >> 4, j = (i & 15) + p.hyp_off;
+      sE[f * kMmaES + (i & 15)] = (f < nt_blk && j < NHP) ? p.w.EA[((int64_t)u * p.T + (tb - 1 + f)) * NHP + j] : 0.f;
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(kMmaConsumers) : "memory");
+    for (int f0 = 0; f0 < nt_blk; f0 += 8) {
+      // A fragments: hypotheses gid / gid + 8, frames f0 + tig / f0 + tig + 4
+      uint32_t ah[4], al[4];
+      {
+        const float* e = sE + (f0 + tig) * kMmaES + gid;
+        tf32_split(e[0], ah[0], al[0]);
+        tf32_split(e[8], ah[1], al[1]);
+        tf32_split(e[4 * kMmaES], ah[2], al[2]);
+        tf32_split(e[4 * kMmaES + 8], ah[3], al[3]);
+      }
+      const int nrow = nt_blk - f0;  // rows of the slot that hold frames (8 except in the last slot)
+      mbar_wait(&full[slot], par);
+      const uint32_t base = ring_u32 + (uint32_t)(slot * 8 * kMmaRow * 4) + b_off;
+      // four n-tiles at a time, phase by phase (the asm statements keep this order): 8 loads in flight, then the
+      // exponentials, the splits, and 12 MMAs that alternate between four accumulators
+      const bool masked = nrow < 8;  // last slot: rows >= nrow were never written by this call (E is zero there,
+                                     // but 0 * NaN is not)
+      const bool keep0 = tig < nrow, keep1 = tig + 4 < nrow;
+#pragma unroll
+      for (int g = 0; g < (DBG == 1 ? 0 : kMmaNT); g += 4) {
+        float xr[8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          xr[2 * q] = mma_lds_f32(base + (g + q) * 32);
+          xr[2 * q + 1] = mma_lds_f32(base + (g + q) * 32 + 4 * kMmaRow * 4);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          xr[2 * q] = ex2f(fmaf(xr[2 * q], B200_LOG2E, -mxl[g + q]));
+          xr[2 * q + 1] = ex2f(fmaf(xr[2 * q + 1], B200_LOG2E, -mxl[g + q]));
+        }
+        if (masked) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (!keep0) xr[2 * q] = 0.f;
+            if (!keep1) xr[2 * q + 1] = 0.f;
+          }
+        }
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) tf32_split(xr[q], hi[q], lo[q]);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) mma_tf32(acc[g + q], al, hi[2 * q], hi[2 * q + 1]);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) mma_tf32(acc[g + q], ah, lo[2 * q], lo[2 * q + 1]);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) mma_tf32(acc[g + q], ah, hi[2 * q], hi[2 * q + 1]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
+      if (++slot == kMmaSlots) { slot = 0; par ^= 1u; }
+    }
+  }
+
+  if (DBG == 1) {  // (developer variant without the arithmetic: keep the exact kernel's queue empty)
+#pragma unroll
+    for (int nt = 0; nt < kMmaNT; ++nt)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[nt][q] = 1.f;
+  }
+  // ---- D fragments: hypotheses gid / gid + 8, tokens wtok + 8*nt + 2*tig + {0,1}
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const int j = gid + 8 * half + p.hyp_off;
+    if (j >= p.n_hyps) continue;
+    const int h = u * p.n_hyps + j;
+    const float sp = p.s_prev ? p.s_prev[h] : 0.f;
+    const int64_t last = p.last_ids[h];
+    const float ma = p.w.MA[h];
+    const float rend = p.w.REND[h];
+#pragma unroll
+    for (int nt = 0; nt < kMmaNT; ++nt) {
+      const int c0 = tile0 + wtok + 8 * nt + 2 * tig;
+      if (c0 >= p.V) continue;  // (V is even: c0 + 1 < V as well)
+      const float2 mx = *reinterpret_cast<const float2*>(p.xmax + (int64_t)u * p.V + c0);
+      float2 x0 = make_float2(B200_LZ, B200_LZ);  // r[0,n] = x[0,c]
+      if (p.output_len == 0) x0 = *reinterpret_cast<const float2*>(p.x + (int64_t)u * p.T * p.V + c0);
+      const float a[2] = {acc[nt][2 * half], acc[nt][2 * half + 1]};
+      const float mxs[2] = {mx.x, mx.y}, x0s[2] = {x0.x, x0.y};
+      float psi[2];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int c = c0 + q;
+        if (c == p.blank) {
+          psi[q] = B200_LZ;
+        } else if (c == p.eos) {
+          psi[q] = rend;
+        } else {
+          psi[q] = finish_psi(a[q], ma + mxs[q], x0s[q]);
+          if ((int64_t)c != last) score_flag(p, a[q], h, c);
+        }
+      }
+      float* lp = p.log_psi + (int64_t)h * p.V + c0;
+      float* sc = p.scores + (int64_t)h * p.V + c0;
+      if ((last == c0 || last == c0 + 1) && last != p.blank && last != p.eos) {
+        // the repeated-last-label entry belongs to the extra row of CTAs
+        const int q = last == c0 ? 1 : 0;
+        lp[q] = psi[q];
+        sc[q] = psi[q] - sp;
+      } else {
+        *reinterpret_cast<float2*>(lp) = make_float2(psi[0], psi[1]);
+        *reinterpret_cast<float2*>(sc) = make_float2(psi[0] - sp, psi[1] - sp);
+      }
+    }
+  }
+}
+
+}  // namespace b200

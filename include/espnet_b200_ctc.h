@@ -182,6 +182,10 @@ int b200_ctc_stage_labels_pinned(const int64_t* targets_host, int64_t n_targets,
  * Process-wide; returns the previous setting. */
 int b200_ctc_debug_force_log_sweep(int on);
 
+/* Developer switch: on != 0 makes b200_ctc_prefix_score use its fp32 score kernels instead of the
+ * tensor-core one (A/B timing; the tests run both). */
+void b200_ctc_debug_prefix_fp32_score(int on);
+
 /* Number of utterances of the last _forward / _fwd_bwd call on `workspace` whose targets were
  * invalid: a label outside [0,V), a label equal to blank, or olen[b] > Lmax.  torch.nn.CTCLoss
  * raises for such input on the CPU (espnet2/asr/ctc.py:49 calls it); here the kernels clamp the

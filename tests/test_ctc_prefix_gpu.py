@@ -16,6 +16,17 @@ pytestmark = pytest.mark.gpu
 ATOL = 1e-4
 
 
+@pytest.fixture(autouse=True, params=["mma", "fp32"])
+def score_kernel(request):
+    """Every test runs with the tensor-core score kernel (the default) and with the fp32 score kernels."""
+    from espnet_b200 import _lib
+
+    lib = _lib.load()
+    lib.b200_ctc_debug_prefix_fp32_score(1 if request.param == "fp32" else 0)
+    yield request.param
+    lib.b200_ctc_debug_prefix_fp32_score(0)
+
+
 def _close(got, ref, atol=ATOL):
     got, ref = np.asarray(got, dtype=np.float64), np.asarray(ref, dtype=np.float64)
     real = np.abs(ref) < 1e9

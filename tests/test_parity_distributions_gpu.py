@@ -199,10 +199,16 @@ def _close(got, ref, atol=ATOL, tag=None, ulps=2):
 
 
 def _walk_vs_reference_th(c, nsteps, snum=0, margin=0, seed=0, tag=None, follow=True):
-    if _domain[0] == "log":
-        pytest.skip("prefix scoring does not depend on the loss sweeps: run once")
+    # (prefix scoring does not depend on the loss sweeps: the second run of every test takes the fp32 score kernels
+    #  instead of the tensor-core one)
+    from espnet_b200 import _lib
     from espnet_b200.ctc_prefix_score import CTCPrefixScoreB200
     from tests._walk import walk_vs_reference_th
+
+    fp32 = _domain[0] == "log"
+    _lib.load().b200_ctc_debug_prefix_fp32_score(1 if fp32 else 0)
+    if tag:
+        tag = tag + ("_fp32" if fp32 else "_mma")
 
     class Ours(object):
         def __init__(self, lp, xlens, eos, margin):
@@ -216,9 +222,13 @@ def _walk_vs_reference_th(c, nsteps, snum=0, margin=0, seed=0, tag=None, follow=
             so = self.impl.index_select_state(st, best.cuda())
             return so, so[0].cpu().numpy(), so[1].cpu().numpy()
 
-    walk_vs_reference_th(c, nsteps, Ours, snum=snum, margin=margin, seed=seed, follow=follow, device="cuda",
-                         close=lambda got, ref, step, what="scores": _close(
-                             got, ref, tag=tag and what == "scores" and f"{tag}_step{step}", ulps=2 if what == "scores" else 6))
+    try:
+        walk_vs_reference_th(c, nsteps, Ours, snum=snum, margin=margin, seed=seed, follow=follow, device="cuda",
+                             close=lambda got, ref, step, what="scores": _close(
+                                 got, ref, tag=tag and what == "scores" and f"{tag}_step{step}",
+                                 ulps=2 if what == "scores" else 6))
+    finally:
+        _lib.load().b200_ctc_debug_prefix_fp32_score(0)
 
 
 @pytest.mark.parametrize("kind", ["scale8", "scale30", "trained", "mismatch", "level"])
