@@ -584,15 +584,42 @@ __device__ __forceinline__ void select_pair(const SelectParams& p, int k, int& h
   }
 }
 
-// ONE WARP per survivor: lane i loads the inputs of frame t0 + i of a batch of 32 frames (and
-// computes phi for it), the next batch is loaded before the current one is consumed, and the recursion itself
-// runs in every lane, taking the inputs of frame f from lane f by shuffle; lane f keeps the values of frame f
-// and stores them after the batch.  The per-thread kernel above waits one DRAM latency per 8 frames (its loads
-// are 20 KB apart); here 64 frames are in flight per survivor and the chain is ex2 -> lg2 only.
+// ONE WARP per survivor: lane i loads the inputs of frame t0 + i of a batch of 32 frames (and computes phi for it),
+// the next batch is loaded before the current one is consumed, and the recursion itself runs in every lane; lane f
+// keeps the values of frame f and stores them after the batch.
+// The recursion is one latency chain per survivor, so its length is what the kernel costs (measured at C3: 157
+// cycles per frame with the inputs fetched by shuffles right in front of their use and the two states computed one
+// after the other).  Here the batch's inputs go through shared memory (one broadcast 16-byte load per frame, issued a
+// frame ahead), each state's chain is  sub -> mul -> ex2 -> add -> lg2 -> fma  (the maximum and the frame's log-prob
+// are folded into the fma's addend, off the chain), and the two states' ex2 / lg2 are issued alternately.
+__device__ __forceinline__ float sel_ex2(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sel_lg2(float x) {
+  float y;
+  asm volatile("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// one frame: (pn, pb) <- (lse(pn, phi) + xc, lse(pn, pb) + xb), natural-log units
+__device__ __forceinline__ void select_frame(float& pn, float& pb, const float4 in) {
+  const float dn = pn - in.x, db = pn - pb;
+  const float basen = fmaxf(pn, in.x) + in.y, baseb = fmaxf(pn, pb) + in.z;
+  const float en = sel_ex2(-fabsf(dn) * B200_LOG2E);
+  const float eb = sel_ex2(-fabsf(db) * B200_LOG2E);
+  const float ln = sel_lg2(1.0f + en);
+  const float lb = sel_lg2(1.0f + eb);
+  pn = fmaf(ln, B200_LN2, basen);
+  pb = fmaf(lb, B200_LN2, baseb);
+}
+
 __global__ void __launch_bounds__(128) prefix_select_warp_kernel(SelectParams p) {
+  __shared__ __align__(16) float4 s_in[4][32];  // per warp: {phi, x[c], x[blank], -} of the 32 frames of a batch
   const int lane = threadIdx.x & 31;
   const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (k >= p.n_new) return;
+  float4* sw = s_in[threadIdx.x >> 5];
   int h, c;
   select_pair(p, k, h, c);
   const int u = h / p.n_hyps;
@@ -620,28 +647,26 @@ __global__ void __launch_bounds__(128) prefix_select_warp_kernel(SelectParams p)
     for (int t0 = p.start; t0 < p.end; t0 += 32) {
       const In nxt = load(t0 + 32);
       const float phi_l = is_last ? cur.rb : lse2_nat(cur.rn, cur.rb);
+      __syncwarp();  // every lane is done with the previous batch
+      sw[lane] = make_float4(phi_l, cur.xc, cur.xb, 0.f);
+      __syncwarp();
       float my_n = B200_LZ, my_b = B200_LZ;
       const int nf = min(32, p.end - t0);
+      float4 in = sw[0];
       if (nf == 32) {
 #pragma unroll
         for (int f = 0; f < 32; ++f) {
-          const float phi = __shfl_sync(0xffffffffu, phi_l, f);
-          const float xc = __shfl_sync(0xffffffffu, cur.xc, f);
-          const float xb = __shfl_sync(0xffffffffu, cur.xb, f);
-          const float nn = lse2_nat(pn, phi) + xc;
-          const float nb = lse2_nat(pn, pb) + xb;
-          pn = nn; pb = nb;
+          const float4 nin = sw[(f + 1) & 31];  // (next frame's inputs: off the chain)
+          select_frame(pn, pb, in);
           if (lane == f) { my_n = pn; my_b = pb; }
+          in = nin;
         }
       } else {
         for (int f = 0; f < nf; ++f) {
-          const float phi = __shfl_sync(0xffffffffu, phi_l, f);
-          const float xc = __shfl_sync(0xffffffffu, cur.xc, f);
-          const float xb = __shfl_sync(0xffffffffu, cur.xb, f);
-          const float nn = lse2_nat(pn, phi) + xc;
-          const float nb = lse2_nat(pn, pb) + xb;
-          pn = nn; pb = nb;
+          const float4 nin = sw[(f + 1) & 31];
+          select_frame(pn, pb, in);
           if (lane == f) { my_n = pn; my_b = pb; }
+          in = nin;
         }
       }
       if (lane < nf) {

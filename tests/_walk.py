@@ -1,6 +1,7 @@
 """A seeded hypothesis walk that drives a prefix scorer under test and the REFERENCE's CTCPrefixScoreTH
 (oracle/_ref, staged by oracle/stage_ref.py) side by side, comparing scores and selected states at every step."""
 import pytest
+import numpy as np
 import torch
 
 
@@ -8,7 +9,8 @@ def walk_vs_reference_th(c, nsteps, make_ours, snum=0, margin=0, seed=0, follow=
     """make_ours(lp, xlens, eos, margin) -> object with
          step(y, state, ids, att) -> (scores numpy (n_bh,V), state)
          select(state, best (B,H)) -> (next state, r numpy (T,2,n_bh), s numpy (n_bh,))
-    close(got, ref, step) asserts."""
+    close(got, ref, step, what="scores", mag=None) asserts; mag: magnitude of the operands a score is the difference
+    of (score = log_psi - s_prev: its float32 resolution is that of log_psi, not of the difference)."""
     from oracle import stage_ref
 
     if not stage_ref.activate():
@@ -38,7 +40,9 @@ def walk_vs_reference_th(c, nsteps, make_ours, snum=0, margin=0, seed=0, follow=
             att[torch.arange(B * H), centre] = 1.0
         s1, st1 = ours.step(y, so, ids, att)
         s2, st2 = ref(y, sr, None if ids is None else ids.to(device), None if att is None else att.to(device))
-        close(s1, s2.cpu().numpy(), step)
+        lpsi = st2[1].detach().cpu().numpy()
+        live = np.abs(lpsi) < 1e9
+        close(s1, s2.cpu().numpy(), step, "scores", float(np.abs(lpsi[live]).max()) if live.any() else 0.0)
         hyp = torch.randint(0, H, (B, H), generator=g)
         if ids is None:
             tok = torch.randint(1, V - 1, (B, H), generator=g)

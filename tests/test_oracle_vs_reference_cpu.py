@@ -13,7 +13,7 @@ from tests._walk import walk_vs_reference_th
 needs_ref = pytest.mark.skipif(stage_ref.path() is None, reason="oracle/_ref is not staged")
 
 
-def _close(got, ref, step=None, what="scores", atol=1e-4):
+def _close(got, ref, step=None, what="scores", mag=None, atol=1e-4):
     got, ref = np.asarray(got, dtype=np.float64), np.asarray(ref, dtype=np.float64)
     real = np.abs(ref) < 1e9
     assert (got[~real] < -1e9).all() and (got[real] > -1e9).all()

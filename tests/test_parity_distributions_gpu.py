@@ -182,7 +182,7 @@ def test_linear_sweeps_certify_ordinary_input_and_hand_over_the_rest(sweep_domai
 ATOL = 1e-4
 
 
-def _close(got, ref, atol=ATOL, tag=None, ulps=2):
+def _close(got, ref, atol=ATOL, tag=None, ulps=2, mag=None):
     """atol absolute, plus `ulps` float32 spacings of the value itself: forward variables and eos scores reach
     magnitudes of several thousand, where one float32 spacing is 5e-4 and two float32 evaluations in different
     operation order (the reference's included) differ by a few of them."""
@@ -192,7 +192,8 @@ def _close(got, ref, atol=ATOL, tag=None, ulps=2):
     assert (got[real] > -1e9).all(), "an entry the reference computes is the log(0) sentinel here"
     if real.any():
         err = np.abs(got[real] - ref[real])
-        tol = atol + ulps * 1.2e-7 * np.abs(ref[real])
+        # (mag: a score is log_psi - s_prev, two numbers of that magnitude: its float32 spacing is theirs)
+        tol = atol + ulps * 1.2e-7 * np.maximum(np.abs(ref[real]), mag or 0.0)
         if tag:
             _report(test=tag, max_abs_err=float(err.max()), max_abs_ref=float(np.abs(ref[real]).max()))
         assert (err <= tol).all(), float((err - tol).max())
@@ -224,9 +225,9 @@ def _walk_vs_reference_th(c, nsteps, snum=0, margin=0, seed=0, tag=None, follow=
 
     try:
         walk_vs_reference_th(c, nsteps, Ours, snum=snum, margin=margin, seed=seed, follow=follow, device="cuda",
-                             close=lambda got, ref, step, what="scores": _close(
+                             close=lambda got, ref, step, what="scores", mag=None: _close(
                                  got, ref, tag=tag and what == "scores" and f"{tag}_step{step}",
-                                 ulps=2 if what == "scores" else 6))
+                                 ulps=2 if what == "scores" else 6, mag=mag))
     finally:
         _lib.load().b200_ctc_debug_prefix_fp32_score(0)
 
