@@ -277,6 +277,54 @@ def workload_config(args, world):
 
 
 # ----------------------------------------------------------------------------------------------- prefix scoring
+def bench_decode_loop(dev, margin=0, pre_beam=None):
+    """The whole multi-utterance search loop at BASELINE config 3 (B=32 utterances x beam 10, T=500, V=5000,
+    ctc_weight 0.3): espnet_b200.recog_batch.recognize_beam_batch = CTC prefix scorer + top-k + state gathers +
+    ended-hypothesis bookkeeping (decoders.py:776-960), driven by a toy attention decoder (embedding -> linear ->
+    log-softmax, attention weights = a window that moves with the output position).  Reported as output positions
+    per second of the WHOLE loop; the toy decoder's own kernels are inside the number."""
+    from espnet_b200.recog_batch import DecoderStep, recognize_beam_batch
+    from tests import _cases
+
+    B, H, T_, V_, L = 32, 10, 500, 5000, 24
+    c = _cases.make_prefix_case(B, T_, V_, H, seed=1238, nsteps=1, kind="trained", min_ratio=0.6, L=L)
+    lpz = c["lp"].to(dev)
+    g = torch.Generator().manual_seed(1239)
+    emb = (torch.randn(V_, 64, generator=g) * 0.3).to(dev)
+    proj = (torch.randn(64, V_, generator=g) * 0.3).to(dev)
+    frames = torch.arange(T_, device=dev, dtype=torch.float32).view(1, -1)
+
+    class Toy(DecoderStep):
+        def start(self, n_bb):
+            return 0
+
+        def step(self, vy, pos):
+            logp = torch.log_softmax(emb[vy] @ proj, dim=1)
+            centre = min(8.0 + 14.0 * pos, T_ - 1.0)
+            att = torch.softmax(-0.05 * (frames - centre) ** 2, dim=1).expand(vy.numel(), T_)
+            return logp, att, pos + 1
+
+        def select(self, pos, vidx):
+            return pos
+
+    def run():
+        stats = {}
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = recognize_beam_batch(Toy(), lpz, c["xlens"], H, V_ - 1, V_ - 1, ctc_weight=0.3, nbest=1, ctc_margin=margin,
+                                   pre_beam=pre_beam, stats=stats)
+        torch.cuda.synchronize()
+        return stats["steps"], time.perf_counter() - t0, out
+
+    run()                      # warm-up (allocator, first launches)
+    n, dt, out = run()
+    return {"metric": "decode_loop_positions_per_sec", "value": n / dt, "unit": "output positions/s", "us_per_position": 1e6 * dt / n,
+            "positions": n, "best_len_utt0": len(out[0][0]["yseq"]),
+            "config": {"workload": f"C3 search loop: B=32 x beam 10, T=500, V=5000, ctc_weight 0.3, margin={margin}, "
+                                   + (f"pre-beam {pre_beam}" if pre_beam else "all tokens scored")
+                                   + ", toy attention decoder, one device->host copy per position"}}
+
+
 def bench_prefix(dev, peak, steps=20, snum=0):
     """Second half of the metric: CTC prefix-score steps/s at BASELINE config 3 (B=32 utterances x beam 10, T=500,
     V=5000, fp32 log-probs).  snum=0: full-vocabulary scoring as recognize_beam_batch does on CUDA; snum=15:
@@ -628,7 +676,7 @@ def run_b200(args, rank, world, local_rank):
             cpu_c1 = cpu_c1_reference(cores)
         except Exception as e:
             cpu_c1 = {"error": str(e)[:200]}
-    prefix = prefix15 = None
+    prefix = prefix15 = decode_loop = None
     ref_gpu = None
     if world == 1:
         x_dev.grad = None
@@ -644,6 +692,10 @@ def run_b200(args, rank, world, local_rank):
         torch.cuda.empty_cache()
         prefix = bench_prefix(dev, peak)
         prefix15 = bench_prefix(dev, peak, snum=15)
+        try:
+            decode_loop = [bench_decode_loop(dev), bench_decode_loop(dev, margin=40), bench_decode_loop(dev, pre_beam=15)]
+        except Exception as e:  # a reported extra, never the reason the line is missing
+            decode_loop = {"error": str(e)[:200]}
     kernels = ["ctc_stream_kernel", "ctc_prep_kernel (under the stream kernel)", "ctc_sweep kernel (alpha+beta)",
                "ctc_occ_kernel<PATCH>", "ctc_grad_rescale_kernel (backward: verifies the upstream scale)"]
     line = {"metric": "ctc_loss_fwd_bwd_utterances_per_sec", "value": value, "unit": "utterances/s",
@@ -654,7 +706,7 @@ def run_b200(args, rank, world, local_rank):
             "host_issue_us_per_step": 1e6 * host_issue_s / args.steps, "cpu_affinity": affinity,
             "roofline": roofline, "roofline_step": roofline_step, "raw_abi": raw_abi,
             "cpu_baseline": cpu, "cpu_reference_c1": cpu_c1, "reference_gpu": ref_gpu, "loss": loss_value,
-            "prefix": prefix, "prefix_pre_beam": prefix15}
+            "prefix": prefix, "prefix_pre_beam": prefix15, "decode_loop": decode_loop}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

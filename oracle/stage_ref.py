@@ -33,9 +33,12 @@ FILES = [
     "espnet/nets/scorers/length_bonus.py",
     "espnet/nets/pytorch_backend/ctc.py",
     "espnet/nets/pytorch_backend/nets_utils.py",
+    "espnet/nets/pytorch_backend/rnn/decoders.py",      # recognize_beam_batch: the multi-utterance search loop (8f4)
+    "espnet/nets/pytorch_backend/rnn/attentions.py",
     "espnet2/asr/ctc.py",
 ]
-PACKAGES = ["espnet", "espnet/nets", "espnet/nets/scorers", "espnet/nets/pytorch_backend", "espnet2", "espnet2/asr"]
+PACKAGES = ["espnet", "espnet/nets", "espnet/nets/scorers", "espnet/nets/pytorch_backend", "espnet/nets/pytorch_backend/rnn",
+            "espnet2", "espnet2/asr"]
 # e2e_asr_common imports the transducer search at module level (never used by end_detect); its dependency tree
 # (transducer utils, espnet2 decoders) is not part of this path, so a one-line stand-in is written instead
 STUBS = {"espnet/nets/beam_search_transducer.py": "class BeamSearchTransducer:  # stand-in, see oracle/stage_ref.py\n    pass\n"}

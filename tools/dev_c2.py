@@ -7,7 +7,7 @@ from espnet_b200 import _lib
 import os
 if os.environ.get("B200_LIN"):
     _lib.load().b200_ctc_debug_force_log_sweep(0)
-B, T, V, L = 64, 500, 5000, 150
+B, T, V, L = (16, 4000, 5000, 1000) if os.environ.get("B200_C5") else (64, 500, 5000, 150)
 dt = torch.bfloat16 if len(sys.argv) < 2 or sys.argv[1] == "bf16" else torch.float32
 full = len(sys.argv) > 2 and sys.argv[2] == "full"
 n = int(sys.argv[3]) if len(sys.argv) > 3 else 20
