@@ -204,6 +204,55 @@ def gpu_reference_pass(batch, dev, steps=10):
                     "-> torch.nn.CTCLoss(sum)/B -> backward (espnet2/asr/ctc.py:46-52 as it runs under autocast)"}
 
 
+def bench_c5_leg(dev, peak, steps=20):
+    """BASELINE config 5 (long form: B=16, T=4000, V=5000, L<=1000, bf16) inside the default line: the plugin call
+    CTC(ctc_type="b200").loss_fn + loss.backward() on device-resident logits, and the reference's call on the same
+    GPU.  (`python bench.py --config c5` runs the full protocol on this configuration.)"""
+    from espnet_b200.ctc import CTC
+
+    cfg = CONFIGS["c5"]
+    batch = make_batch(cfg, 1239)
+    tg = torch.cat([batch["ys"][b, : int(batch["olen"][b])] for b in range(cfg["B"])])
+    x = batch["x"].to(dev).requires_grad_()
+    ctc = CTC(cfg["V"], 8, ctc_type="b200")
+
+    def one():
+        x.grad = None
+        loss = ctc.loss_fn(x.transpose(0, 1), tg, batch["ilen"], batch["olen"])
+        loss.backward()
+        return loss
+
+    for _ in range(3):
+        one()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss = one()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    nbytes = 2 * cfg["B"] * cfg["T"] * cfg["V"] * 2       # logits read once + gradient written once
+    lattice = 2 * 4 * int(batch["ilen"].sum()) * (2 * cfg["L"] + 8)   # alpha + beta rows, written once and read once
+    gbs = nbytes / (ms * 1e-3) / 1e9
+    out = {"workload": cfg["name"], "value": cfg["B"] / (ms * 1e-3), "unit": "utterances/s", "ms_per_step": ms, "steps": steps,
+           "loss": float(loss.detach()), "algorithmic_bytes": nbytes, "lattice_bytes_alpha_plus_beta": lattice,
+           "roofline_step": {"achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                             "frac_with_lattice_traffic": (nbytes + 2 * lattice) / (ms * 1e-3) / 1e9 / peak},
+           "note": "lattice sweeps: 4-CTA thread-block clusters per (utterance, direction), hand-off through distributed "
+                   "shared memory"}
+    x.grad = None
+    del x
+    torch.cuda.empty_cache()
+    try:
+        out["reference_gpu"] = gpu_reference_pass(batch, dev, steps=3)
+        out["reference_gpu"].pop("what", None)
+    except Exception as e:  # reported baseline only
+        out["reference_gpu"] = {"error": str(e)[:200]}
+    torch.cuda.empty_cache()
+    return out
+
+
 def cpu_oracle_pass(batch, n_utt):
     """The C restatement (oracle/ctc_oracle.c), one utterance per OpenMP thread."""
     import numpy as np
@@ -676,7 +725,7 @@ def run_b200(args, rank, world, local_rank):
             cpu_c1 = cpu_c1_reference(cores)
         except Exception as e:
             cpu_c1 = {"error": str(e)[:200]}
-    prefix = prefix15 = decode_loop = None
+    prefix = prefix15 = decode_loop = c5 = None
     ref_gpu = None
     if world == 1:
         x_dev.grad = None
@@ -693,6 +742,10 @@ def run_b200(args, rank, world, local_rank):
         prefix = bench_prefix(dev, peak)
         prefix15 = bench_prefix(dev, peak, snum=15)
         try:
+            c5 = bench_c5_leg(dev, peak)
+        except Exception as e:  # a reported extra, never the reason the line is missing
+            c5 = {"error": str(e)[:200]}
+        try:
             decode_loop = [bench_decode_loop(dev), bench_decode_loop(dev, margin=40), bench_decode_loop(dev, pre_beam=15)]
         except Exception as e:  # a reported extra, never the reason the line is missing
             decode_loop = {"error": str(e)[:200]}
@@ -706,7 +759,7 @@ def run_b200(args, rank, world, local_rank):
             "host_issue_us_per_step": 1e6 * host_issue_s / args.steps, "cpu_affinity": affinity,
             "roofline": roofline, "roofline_step": roofline_step, "raw_abi": raw_abi,
             "cpu_baseline": cpu, "cpu_reference_c1": cpu_c1, "reference_gpu": ref_gpu, "loss": loss_value,
-            "prefix": prefix, "prefix_pre_beam": prefix15, "decode_loop": decode_loop}
+            "prefix": prefix, "prefix_pre_beam": prefix15, "decode_loop": decode_loop, "c5": c5}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

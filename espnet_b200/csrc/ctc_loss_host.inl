@@ -401,6 +401,8 @@ extern "C" int b200_ctc_stage_labels_pinned(const int64_t* targets_host, int64_t
   return B200_OK;
 }
 
+extern "C" void b200_ctc_debug_single_cta_sweep(int on) { g_single_cta_sweep = on ? 1 : 0; }
+
 extern "C" int b200_ctc_loss_status(const void* workspace, int64_t T, int64_t B, int64_t V, int64_t Lmax,
                                     int32_t* n_invalid_host, int32_t* n_redone_host, void* stream) {
   B200_CHECK_ARG(workspace && n_invalid_host, B200_ERR_INVALID_ARGUMENT, "null pointer argument");

@@ -743,10 +743,16 @@ extern "C" int b200_debug_sweep_clocks(long long* host) {
 namespace b200 {
 #endif
 
+}  // namespace b200
+#include "ctc_loss_sweep_cluster.inl"
+namespace b200 {
+static int g_single_cta_sweep = 0;  // developer switch: long label sequences in one CTA (b200_ctc_debug_single_cta_sweep)
+
 // pdl: staged under the stream kernel of the same call
 static int launch_sweep(const LossParams& p, cudaStream_t st, bool pdl = false) {
   const int threads = (int)align_up((size_t)(p.Lmax + 1), 32);
   if (threads <= 256) return launch_sweep_staged(p, threads, st, pdl);
+  if (!g_single_cta_sweep) return launch_sweep_cluster(p, st, pdl);
   return launch_sweep_t<4, 1024>(p, threads, st, pdl);
 }
 

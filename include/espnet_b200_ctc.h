@@ -182,6 +182,10 @@ int b200_ctc_stage_labels_pinned(const int64_t* targets_host, int64_t n_targets,
  * Process-wide; returns the previous setting. */
 int b200_ctc_debug_force_log_sweep(int on);
 
+/* Developer switch: on != 0 runs the lattice sweeps of utterances with 256 <= Lmax + 1 <= 1024 in one CTA per
+ * (utterance, direction) instead of a 4-CTA thread-block cluster (A/B timing; the tests run both). */
+void b200_ctc_debug_single_cta_sweep(int on);
+
 /* Developer switch: on != 0 makes b200_ctc_prefix_score use its fp32 score kernels instead of the
  * tensor-core one (A/B timing; the tests run both). */
 void b200_ctc_debug_prefix_fp32_score(int on);

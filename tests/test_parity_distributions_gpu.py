@@ -33,9 +33,13 @@ def sweep_domain(request):
 
     lib = _lib.load()
     was = lib.b200_ctc_debug_force_log_sweep(1 if request.param == "log" else 0)
+    # (long label sequences, L > 255, have no linear-domain sweep: their second run takes the one-CTA sweep kernel
+    #  instead of the thread-block-cluster one)
+    lib.b200_ctc_debug_single_cta_sweep(1 if request.param == "log" else 0)
     _domain[0] = request.param
     yield request.param
     lib.b200_ctc_debug_force_log_sweep(was)
+    lib.b200_ctc_debug_single_cta_sweep(0)
 
 
 _domain = ["?"]
