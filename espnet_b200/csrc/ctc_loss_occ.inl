@@ -440,10 +440,16 @@ static int launch_occ_nj(const LossParams& p, cudaStream_t st) {
   return B200_OK;
 }
 
+}  // namespace b200
+#include "ctc_loss_occ_wide.inl"
+namespace b200 {
+
 template <typename T, bool PATCH, bool LIN>
 static int launch_occ_t(const LossParams& p, cudaStream_t st) {
   if (p.Lmax + 1 <= 32 * 5) return launch_occ_nj<T, PATCH, 5, LIN>(p, st);
   if (LIN || p.Lmax + 1 <= 32 * 10) return launch_occ_nj<T, PATCH, 10, LIN>(p, st);  // (LIN: Lmax <= 255)
+  // long rows: a CTA per row (developer switch b200_ctc_debug_single_cta_sweep: the warp-per-row kernel)
+  if (!LIN && p.Lmax + 1 <= kWideThreads * kWideIter && !g_single_cta_sweep) return launch_occ_wide<T, PATCH>(p, st);
   return launch_occ_nj<T, PATCH, 0, LIN>(p, st);
 }
 

@@ -19,6 +19,7 @@ constexpr int kClusterCtas = 4;
 constexpr int kClusterWarps = 8;                              // state warps per CTA
 constexpr int kClusterThreads = kClusterWarps * 32;
 constexpr int kClusterMaxWarps = kClusterCtas * kClusterWarps;  // 32: L + 1 <= 1024
+constexpr int kClusterRing = 512;                               // boundary records per warp (frames)
 
 __device__ __forceinline__ uint32_t cluster_rank() {
   uint32_t r;
@@ -42,7 +43,10 @@ __device__ __forceinline__ void cluster_sync_all() {
 }
 
 __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(LossParams p) {
-  constexpr int CHF = 4, kR = 256, kWR = 128, NWT = kClusterMaxWarps;
+  // chunks of 8 frames (the one-CTA kernel: 4): the per-chunk work -- boundary poll, level record, control arithmetic,
+  // the loads of chunk c + 2 -- is paid half as often; the hand-off ring holds (32 + 3) chunks of skew
+  constexpr int CHF = 8, kR = kClusterRing, kWR = 128, NWT = kClusterMaxWarps;
+  static_assert(kR >= CHF * (kClusterMaxWarps + 3), "hand-off ring");
   extern __shared__ __align__(16) unsigned char sw_smem[];
   Tagged* s_bnd = reinterpret_cast<Tagged*>(sw_smem);          // [1 + kClusterWarps][kR]: row 0 arrives from CTA rank-1
   Tagged* s_wmx = s_bnd + (size_t)(1 + kClusterWarps) * kR;    // [kWR][NWT] level of global warp g at the start of chunk c
@@ -110,14 +114,23 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
       else asm volatile("st.volatile.shared.v2.b32 [%0], {%1,%2};" ::"r"(bdst + (uint32_t)idx * 8u), "f"(v), "r"(tag) : "memory");
     };
     auto frame = [&](float lb_t, float ll_t, float bn, float o, int fr) {
+      // (the frame of ctc_sweep_staged_kernel: the skip mask folded into the own-state side, two predicated
+      //  subtractions instead of a select in front of one, the label state's ex2 / lg2 issued first)
       const float sh = __shfl_up_sync(0xffffffffu, al, 1);
-      const float nbr = lane0 ? bn : sh;
       const float hi = fmaxf(al, ab);
       const float s1 = 1.0f + ex2f(-fabsf(al - ab));
-      const float x = lse2_abs(ab, nbr);
-      const float y = lse3_pre(hi, s1, nbr + skipmask);
-      ab = (lb_t - o) + x;
-      al = (ll_t - o) + y;
+      const float hi2 = hi - skipmask;
+      const float lbo = lb_t - o, llo = ll_t - o;
+      const float dl = sub_pick(lane0, bn, sh, hi2);
+      const float db = sub_pick(lane0, bn, sh, ab);
+      const float t = ex2f(-fabsf(dl));
+      const float u = ex2f(-fabsf(db));
+      const float nbr = lane0 ? bn : sh;
+      const float sum = (dl <= 0.f) ? (s1 + t) : fmaf(s1, t, 1.0f);
+      const float mxl = llo + (skip_ok ? fmaxf(hi, nbr) : hi);
+      const float mxb = lbo + fmaxf(ab, nbr);
+      al = mxl + lg2f(sum);
+      ab = mxb + lg2f(1.0f + u);
       if (lane31) put_boundary(fr & (kR - 1), al, fr);
       if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
       outp += ostep;
@@ -266,7 +279,7 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
 }
 
 static size_t sweep_cluster_smem() {
-  return sizeof(Tagged) * (size_t)(1 + kClusterWarps) * 256 + sizeof(Tagged) * 128 * kClusterMaxWarps + sizeof(int) * 128;
+  return sizeof(Tagged) * (size_t)(1 + kClusterWarps) * kClusterRing + sizeof(Tagged) * 128 * kClusterMaxWarps + sizeof(int) * 128;
 }
 
 static int launch_sweep_cluster(const LossParams& p, cudaStream_t st, bool pdl) {
