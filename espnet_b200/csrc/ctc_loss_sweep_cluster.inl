@@ -20,6 +20,7 @@ constexpr int kClusterWarps = 8;                              // state warps per
 constexpr int kClusterThreads = kClusterWarps * 32;
 constexpr int kClusterMaxWarps = kClusterCtas * kClusterWarps;  // 32: L + 1 <= 1024
 constexpr int kClusterRing = 512;                               // boundary records per warp (frames)
+constexpr int kClusterSlack = 8;                                // chunks of slack in the level feedback (see `delay`)
 
 __device__ __forceinline__ uint32_t cluster_rank() {
   uint32_t r;
@@ -33,7 +34,22 @@ __device__ __forceinline__ uint32_t cluster_map(uint32_t local, uint32_t rank) {
   return r;
 }
 __device__ __forceinline__ void stc_tagged(uint32_t addr, float v, int tag) {
-  asm volatile("st.volatile.shared::cluster.v2.b32 [%0], {%1,%2};" ::"r"(addr), "f"(v), "r"(tag) : "memory");
+  // (relaxed, cluster scope: one 8-byte store that is not ordered against the stores before it -- a volatile store
+  //  would make every hand-off wait for the previous one's round trip to the other SM)
+  asm volatile("{\n.reg .b64 q;\nmov.b64 q, {%1,%2};\nst.relaxed.cluster.shared::cluster.b64 [%0], q;\n}" ::"r"(addr), "r"(__float_as_int(v)), "r"(tag) : "memory");
+}
+// generic address of a shared::cluster address (so that the stores below need no per-store window arithmetic)
+__device__ __forceinline__ uint64_t cluster_generic(uint32_t cluster_addr) {
+  uint64_t g;
+  asm volatile("cvta.shared::cluster.u64 %0, %1;" : "=l"(g) : "l"((uint64_t)cluster_addr));
+  return g;
+}
+// {v, tag} as ONE predicated 8-byte store to a generic address (own or a neighbour's shared memory): no branch, so
+// the lane that publishes does not put a divergent region on the warp's chain (measured: 215-240 cycles per frame
+// with `if (lane31) { remote ? ... : ... }`, against ~115 for the recursion itself)
+__device__ __forceinline__ void stg_tagged_if(bool on, uint64_t gaddr, float v, int tag) {
+  asm volatile("{\n.reg .pred p;\n.reg .b64 q;\nsetp.ne.s32 p, %3, 0;\nmov.b64 q, {%1,%2};\n@p st.relaxed.cluster.b64 [%0], q;\n}"
+               ::"l"(gaddr), "r"(__float_as_int(v)), "r"(tag), "r"((int)on) : "memory");
 }
 __device__ __forceinline__ void stc_f32(uint32_t addr, float v) {
   asm volatile("st.volatile.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
@@ -46,7 +62,7 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
   // chunks of 8 frames (the one-CTA kernel: 4): the per-chunk work -- boundary poll, level record, control arithmetic,
   // the loads of chunk c + 2 -- is paid half as often; the hand-off ring holds (32 + 3) chunks of skew
   constexpr int CHF = 8, kR = kClusterRing, kWR = 128, NWT = kClusterMaxWarps;
-  static_assert(kR >= CHF * (kClusterMaxWarps + 3), "hand-off ring");
+  static_assert(kR >= CHF * (kClusterMaxWarps + kClusterSlack + 3) && kWR >= 2 * (kClusterMaxWarps + kClusterSlack) + 4, "rings");
   extern __shared__ __align__(16) unsigned char sw_smem[];
   Tagged* s_bnd = reinterpret_cast<Tagged*>(sw_smem);          // [1 + kClusterWarps][kR]: row 0 arrives from CTA rank-1
   Tagged* s_wmx = s_bnd + (size_t)(1 + kClusterWarps) * kR;    // [kWR][NWT] level of global warp g at the start of chunk c
@@ -102,17 +118,25 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
     const Tagged* bsrc = s_bnd + (size_t)warp * kR;  // row w: what the warp before this one published
     // where this warp publishes: the next local row, or row 0 of the next CTA
     const bool remote = warp == kClusterWarps - 1 && gw + 1 < nwa;
-    const uint32_t bdst = remote ? cluster_map(smem_u32(s_bnd), rank + 1) : smem_u32(s_bnd + (size_t)(warp + 1) * kR);
-    const uint32_t wmx_local = smem_u32(s_wmx);
-    const int delay = nwa;
+    const uint64_t bdst = remote ? cluster_generic(cluster_map(smem_u32(s_bnd), rank + 1))
+                                 : reinterpret_cast<uint64_t>(s_bnd + (size_t)(warp + 1) * kR);
+    // lane r < nca publishes this warp's level records into CTA r of the cluster
+    const uint64_t wmx_dst = cluster_generic(cluster_map(smem_u32(s_wmx), (uint32_t)(lane < nca ? lane : 0))) + (uint64_t)gw * 8u;
+    // The level record of chunk c - delay must be there when chunk c starts.  Successive warps run one chunk apart, so
+    // the last warp is nwa - 1 chunks (plus three hops between SMs) behind the first: with delay = nwa the first warp
+    // would wait for the last one at every second chunk and the whole ring of dependencies would set the pace.
+    const int delay = nwa + kClusterSlack;
+#ifdef B200_SWEEP_CLOCKS
+    // developer instrumentation: SM clock at four points of chunks 64..127 for eight warps of the longest utterance
+    const int clk_slot = gw == 0 ? 0 : gw == 1 ? 1 : gw == 7 ? 2 : gw == 8 ? 3 : gw == 9 ? 4 : gw == 16 ? 5 : gw == 24 ? 6 : gw == 31 ? 7 : -1;
+#define CL_STAMP(k) do { if (blockIdx.x == 0 && lane == 0 && clk_slot >= 0 && c >= 64 && c < 128) g_sweep_clk[((d * 8 + clk_slot) * 4 + (k)) * 64 + (c - 64)] = clock64(); } while (0)
+#else
+#define CL_STAMP(k) do { } while (0)
+#endif
     float dstep = 0.f;
     float xprev = 0.f; int sprev = 0;
     bool have_prev = false;
 
-    auto put_boundary = [&](int idx, float v, int tag) {  // (lane 31; `remote` is uniform over the warp)
-      if (remote) stc_tagged(bdst + (uint32_t)idx * 8u, v, tag);
-      else asm volatile("st.volatile.shared.v2.b32 [%0], {%1,%2};" ::"r"(bdst + (uint32_t)idx * 8u), "f"(v), "r"(tag) : "memory");
-    };
     auto frame = [&](float lb_t, float ll_t, float bn, float o, int fr) {
       // (the frame of ctc_sweep_staged_kernel: the skip mask folded into the own-state side, two predicated
       //  subtractions instead of a select in front of one, the label state's ex2 / lg2 issued first)
@@ -131,7 +155,7 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
       const float mxb = lbo + fmaxf(ab, nbr);
       al = mxl + lg2f(sum);
       ab = mxb + lg2f(1.0f + u);
-      if (lane31) put_boundary(fr & (kR - 1), al, fr);
+      stg_tagged_if(lane31, bdst + (uint64_t)((fr & (kR - 1)) * 8), al, fr);
       if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
       outp += ostep;
     };
@@ -141,7 +165,7 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
       float corr = 0.f;
       const float wm = warp_max_redux(fmaxf(ab, al));
       // the level of this warp goes to every active CTA of the cluster (lanes 0 .. nca-1, one CTA each)
-      if (lane < nca) stc_tagged(cluster_map(wmx_local, (uint32_t)lane) + (uint32_t)((c & (kWR - 1)) * NWT + gw) * 8u, wm, c);
+      stg_tagged_if(lane < nca, wmx_dst + (uint64_t)((c & (kWR - 1)) * NWT) * 8u, wm, c);
       if (lane31) s_hist[c & (kWR - 1)] = csum;
       __syncwarp();
       const int delay_p = (delay + kP - 1) / kP * kP;
@@ -189,7 +213,7 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
           const float lb_t = sb[f], ll_t = sl[f];
           if (fr == 0) {
             if (i == 0) { ab = lb_t; al = ll_t; }
-            if (lane31) put_boundary(0, al, 0);
+            stg_tagged_if(lane31, bdst, al, 0);
             if (active) *reinterpret_cast<float2*>(outp) = make_float2(ab, al);
             outp += ostep;
           } else {
@@ -216,12 +240,14 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
     };
     auto fast_chunk = [&](int c, float(&xb)[CHF], float(&xl)[CHF], float(&nb)[CHF], float(&nl)[CHF]) {
       const int f0 = c * CHF;
+      CL_STAMP(0);
       float first = xb[0] + xl[0];
 #pragma unroll
       for (int f = 1; f < CHF; ++f) first += xb[f] + xl[f];
       asm volatile("" ::"f"(first));
       if (c + 2 < nfull) load_chunk(c + 2, nb, nl);
       const float corr = chunk_begin(c, CHF);
+      CL_STAMP(1);
       float bn[CHF];
 #pragma unroll
       for (int f = 0; f < CHF; ++f) bn[f] = B200_NEG;
@@ -237,8 +263,10 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
           }
         } while (!ok);
       }
+      CL_STAMP(2);
 #pragma unroll
       for (int f = 0; f < CHF; ++f) frame(xb[f], xl[f], bn[f], dstep + (f == 0 ? corr : 0.f), f0 + f);
+      CL_STAMP(3);
       csum += CHF * (int)dstep + (int)corr;
     };
 
