@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
       outp += ostep;
     };
     auto chunk_begin = [&](int c, int n) -> float {
-      constexpr int kP = 2;
+      constexpr int kP = 4;  // (the one-CTA kernels: 2; here the per-chunk work sets the pace, see the header)
       if (c % kP) return 0.f;
       float corr = 0.f;
       const float wm = warp_max_redux(fmaxf(ab, al));
