@@ -96,41 +96,67 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.samples)}
 
 
-def pin_to_gpu_numa_node(local_rank, world):
-    """Pins this rank (and therefore the first touch of its pinned host buffers) to the CPU cores next to its GPU,
-    as `nvidia-smi topo -m` reports them ("CPU Affinity" column).  With N ranks uploading 257 MB per step each,
-    unpinned processes put their staging buffers wherever the scheduler ran them first: round 1 measured 52 GB/s of
-    H2D per GPU at N=1 falling to 23 GB/s at N=8.  When every GPU reports the same (whole-machine) affinity the
-    cores are split evenly between the ranks instead.  Returns a description for the JSON line; never raises."""
+def _gpu_cpu_affinity(world):
+    """{gpu index: set of CPU cores next to it} for GPUs 0..world-1, from NVML (`nvmlDeviceGetCpuAffinity`: what the
+    "CPU Affinity" column of `nvidia-smi topo -m` prints).  Eight ranks starting `nvidia-smi topo -m` at once took more
+    than 10 s each on the 8-GPU box; the NVML query is a few milliseconds.  Falls back to parsing that command."""
     try:
-        out = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=10).stdout
-        lines = [ln for ln in out.splitlines() if ln.strip()]
-        hdr = next(ln for ln in lines if "CPU Affinity" in ln)
-        cols = [c.strip() for c in hdr.split("\t")]
-        k = cols.index("CPU Affinity")
-        aff = {}
-        for ln in lines:
-            f = [c.strip() for c in ln.split("\t")]
-            if f and f[0].startswith("GPU") and f[0][3:].isdigit() and len(f) > k:
-                aff[int(f[0][3:])] = f[k]
+        import pynvml
 
-        def cores(spec):
-            s = set()
-            for part in spec.split(","):
-                a, _, b = part.partition("-")
-                s.update(range(int(a), int(b or a) + 1))
-            return s
+        pynvml.nvmlInit()
+        try:
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            order = [int(v) for v in vis.split(",")] if vis and all(v.strip().isdigit() for v in vis.split(",")) else None
+            ncpu = os.cpu_count() or 1
+            words = (max(ncpu, 1) + 63) // 64
+            aff = {}
+            for r in range(world):
+                h = pynvml.nvmlDeviceGetHandleByIndex(order[r] if order else r)
+                mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+                aff[r] = {64 * w + bit for w, m in enumerate(mask) for bit in range(64) if (int(m) >> bit) & 1}
+            return aff, "nvml"
+        finally:
+            pynvml.nvmlShutdown()
+    except Exception:
+        pass
+    out = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=90).stdout
+    lines = [ln for ln in out.splitlines() if ln.strip()]
+    hdr = next(ln for ln in lines if "CPU Affinity" in ln)
+    k = [c.strip() for c in hdr.split("\t")].index("CPU Affinity")
+    aff = {}
+    for ln in lines:
+        f = [c.strip() for c in ln.split("\t")]
+        if f and f[0].startswith("GPU") and f[0][3:].isdigit() and len(f) > k:
+            cores = set()
+            for part in f[k].split(","):
+                lo, _, hi = part.partition("-")
+                cores.update(range(int(lo), int(hi or lo) + 1))
+            aff[int(f[0][3:])] = cores
+    return aff, "nvidia-smi topo -m"
 
-        mine = cores(aff[local_rank]) & os.sched_getaffinity(0)
+
+def pin_to_gpu_numa_node(local_rank, world):
+    """Pins this rank (and therefore the first touch of its pinned host buffers) to the CPU cores next to its GPU.
+    With N ranks uploading 257 MB per step each, unpinned processes put their staging buffers wherever the scheduler
+    ran them first: round 1 measured 52 GB/s of H2D per GPU at N=1 falling to 23 GB/s at N=8; and with one loss
+    exchange per step every rank waits for the slowest host.  GPUs that share one affinity set split its cores evenly
+    between their ranks.  Returns a description for the JSON line; never raises."""
+    try:
+        aff, source = _gpu_cpu_affinity(world)
+        allowed = os.sched_getaffinity(0)
+        mine = aff[local_rank] & allowed
         if not mine:
-            return {"pinned": False, "why": "no usable cores in " + aff[local_rank]}
-        same = world > 1 and len({aff.get(r) for r in range(world)}) == 1
-        if same:   # one affinity for all GPUs: give every rank its own slice of it
+            return {"pinned": False, "why": "no usable cores next to GPU %d" % local_rank, "source": source}
+        sharers = [r for r in range(world) if aff.get(r) == aff[local_rank]]
+        if len(sharers) > 1:   # several GPUs on one node: every rank gets its own slice of the node's cores
             lst = sorted(mine)
-            per = max(1, len(lst) // world)
-            mine = set(lst[local_rank * per:(local_rank + 1) * per]) or mine
+            per = max(1, len(lst) // len(sharers))
+            k = sharers.index(local_rank)
+            mine = set(lst[k * per:(k + 1) * per]) or mine
         os.sched_setaffinity(0, mine)
-        return {"pinned": True, "cores": len(mine), "spec": aff[local_rank], "split_evenly": bool(same)}
+        lst = sorted(mine)
+        return {"pinned": True, "cores": len(mine), "first_core": lst[0], "last_core": lst[-1],
+                "gpus_sharing_the_node": len(sharers), "source": source}
     except Exception as e:
         return {"pinned": False, "why": f"{type(e).__name__}: {e}"[:120]}
 

@@ -32,6 +32,8 @@ class PeerSlots(object):
             raise RuntimeError("symmetric memory rendezvous returned no peer pointers")
         self.ptrs = (ctypes.c_uint64 * self.world)(*ptrs)
         self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._status_ptr = self.status.data_ptr()
+        self._fn = lib.b200_peer_sum_exchange
         self.seq = 0
         torch.cuda.synchronize(self.device)
         dist.barrier(group)   # every ring is zeroed before anyone stores into it
@@ -43,12 +45,20 @@ class PeerSlots(object):
         self.seq += 1
         if self.seq >= 2 ** 31 - 1:
             raise RuntimeError("peer exchange sequence number exhausted")
-        with torch.cuda.device(self.device):
-            rc = _lib.load().b200_peer_sum_exchange(self.ptrs, self.world, self.rank, self.seq, local_sum.data_ptr(),
-                                                    float(sum_scale), float(local_count), pair.data_ptr(),
-                                                    self.status.data_ptr(),
-                                                    torch.cuda.current_stream(self.device).cuda_stream)
-        _lib.check(rc, "b200_peer_sum_exchange")
+        # (lean on purpose: this runs on every training step of every rank -- no device guard when the device is
+        #  already current, raw stream handle)
+        dev = self.device
+        pp = pair.data_ptr()
+        stream = torch._C._cuda_getCurrentRawStream(dev.index)
+        if torch.cuda.current_device() == dev.index:
+            rc = self._fn(self.ptrs, self.world, self.rank, self.seq, local_sum.data_ptr(), float(sum_scale),
+                          float(local_count), pp, self._status_ptr, stream)
+        else:
+            with torch.cuda.device(dev):
+                rc = self._fn(self.ptrs, self.world, self.rank, self.seq, local_sum.data_ptr(), float(sum_scale),
+                              float(local_count), pp, self._status_ptr, stream)
+        if rc:
+            _lib.check(rc, "b200_peer_sum_exchange")
         return pair
 
     def failed(self):
