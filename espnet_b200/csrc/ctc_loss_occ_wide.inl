@@ -133,10 +133,15 @@ __global__ void __launch_bounds__(kWideThreads + 32) ctc_occ_wide_kernel(LossPar
     float wgt = 1.f;
     bool poison = false;
     auto enter = [&]() {  // label columns and duplicate codes of utterance cb (between two CTA-wide barriers)
+      // The utterance's nll (written by its alpha sweep before it signals) decides whether its rows are poisoned: the
+      // consumers wait for the completion flags themselves -- the producer warp's wait orders only ITS copies, and a
+      // consumer can get here before the sweeps of the next utterance have finished (a stale nll from an earlier
+      // call made this decision at random).
+      if (tid == 0) while (ld_acquire_s32(p.ws.done + cb) < 2) __nanosleep(64);
       asm volatile("bar.sync 1, %0;" ::"n"(kWideThreads) : "memory");
       if (PATCH) {
         wgt = p.grad_scale * (p.grad_weight ? p.grad_weight[cb] : 1.0f);
-        poison = !isfinite(p.ws.nll_ws[cb]) || isnan(wgt);
+        poison = !isfinite(ld_cg_f32(p.ws.nll_ws + cb)) || isnan(wgt);
       }
       const int* lab = p.ws.labels + (int64_t)cb * Kp;
       const int* dup = p.ws.dupcode + (int64_t)cb * Kp;

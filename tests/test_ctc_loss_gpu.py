@@ -439,3 +439,40 @@ def test_many_utterances_more_ctas_than_sms():
         np.testing.assert_allclose(nll, rn, rtol=TOL_F32)
         np.testing.assert_allclose(ls, rn.sum(), rtol=TOL_F32)
         assert _normrel(grad, rg) <= TOL_F32
+
+
+@pytest.mark.parametrize("split", [False, True])
+@pytest.mark.parametrize("Lmax", [255, 256, 257, 320, 321, 512, 513, 769, 1023])
+def test_long_label_sequences_at_the_kernel_boundaries(Lmax, split, sweep_domain):
+    """Label lengths around the hand-over points of the long-lattice kernels (staged sweep <= 255 < cluster sweep: 256
+    label positions per CTA of the cluster; register patch kernel <= 319 < CTA-per-row patch kernel), with, in ONE batch:
+    an utterance at Lmax (its last blank and last label state in different CTAs when Lmax is a multiple of 256), a
+    short one (one active CTA in its cluster), an empty target, an infeasible one (inf loss, NaN gradient rows),
+    long runs of a repeated label (skip transitions forbidden, duplicates merged across threads of different warps) and
+    an utterance shorter than one 8-frame chunk."""
+    g = torch.Generator().manual_seed(5000 + Lmax)
+    B, V = 6, 48
+    T = 2 * Lmax + 60
+    x = torch.randn(B, T, V, generator=g) * 2.0
+    ys = torch.randint(1, V, (B, Lmax), generator=g)
+    ys[4, : Lmax // 2] = 7                      # a long run of one label: needs 2 frames per repeat
+    olen = torch.tensor([Lmax, 3, 0, Lmax, Lmax // 2 + 5, 2])
+    ilen = torch.tensor([T, T - 17, 40, Lmax - 1, T, 5])   # utterance 3 is infeasible (fewer frames than labels)
+    nll, grad, _ = _run(x, ilen, olen, ys, split=split)
+    rn, rg = _ref64(x, ilen, olen, ys)
+    fin = np.isfinite(rn)
+    assert list(fin) == [True, True, True, False, True, True]
+    assert (np.isposinf(nll) == ~fin).all()
+    np.testing.assert_allclose(nll[fin], rn[fin], rtol=TOL_F32)
+    assert (np.isnan(grad) == np.isnan(rg)).all()
+    # The tight lattices of this batch (T barely above what the labels need, a forced run of repeats) keep the states
+    # that matter hundreds of log2 units below the frame maximum the sweeps re-centre on: float32 resolves them to
+    # ~1e-5, the reference's own float32 evaluation (no re-centring: |alpha| ~ 4 T) to less.  Bar, as in
+    # test_parity_distributions_gpu._check_loss: 1e-5 or the error of torch's float32 CTC on the same input,
+    # whichever is larger (2e-5 at least for the float64 linear-domain sweeps, Lmax <= 255, 20-bit mantissas).
+    _, fg = _ref64(x, ilen, olen, ys, dt=torch.float32)
+    e_g, e_ref = _normrel(grad, rg), _normrel(fg, rg)
+    print(f"Lmax={Lmax} split={split} {sweep_domain}: grad error {e_g:.2e}, torch float32 {e_ref:.2e}")
+    assert e_g <= max(2e-5 if sweep_domain == "lin" and Lmax <= 255 else TOL_F32, e_ref), (e_g, e_ref)
+    for b in range(B):
+        assert (grad[b, int(ilen[b]):] == 0).all()
