@@ -127,7 +127,7 @@ __device__ __forceinline__ void group_sync(int id, int threads) {
 }
 
 template <typename T, int G>
-__global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(LossParams p, int nslots, int slot_bytes) {
+__global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(LossParams p, int nslots, int slot_bytes, int park_floats) {
   extern __shared__ __align__(128) unsigned char st_smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(st_smem);  // [kStreamMaxSlots]
   uint64_t* empty = full + kStreamMaxSlots;               // [kStreamMaxSlots]
@@ -237,10 +237,11 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
       float xg[kStreamGather];
 #pragma unroll
       for (int g = 0; g < kStreamGather; ++g) xg[g] = ElemTraits<T>::to_float(sT[col[g]]);
-      // (label positions beyond the register slots: raw value parked in the occupancy buffer, which
-      // nobody reads before the patch kernel; lpg itself only ever receives FINAL values, because the
-      // sweeps running under this kernel treat any non-NaN word of lpg as valid)
-      float* park = p.ws.occ + row * Kp;
+      // (label positions beyond the register slots: raw value parked in this row group's strip of shared memory
+      // behind the ring -- in global memory it was 0.4 GB of extra traffic per C5 step; lpg itself only ever
+      // receives FINAL values, because the sweeps running under this kernel treat any non-NaN word of lpg as valid)
+      float* park = reinterpret_cast<float*>(slots + (size_t)nslots * slot_bytes) + (size_t)grp * park_floats -
+                    GT * kStreamGather;
       // largest raw value among the blank / label columns (for the feed-forward scale of the linear sweeps)
       float gx = -3.0e38f;
 #pragma unroll
@@ -397,7 +398,7 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
 }
 
 struct StreamCfg {
-  int nslots, slot_bytes, smem, group;
+  int nslots, slot_bytes, smem, group, park_floats;
 };
 
 // The one-pass kernel needs whole rows resident in shared memory and 16-byte aligned rows.
@@ -413,6 +414,13 @@ static bool plan_stream(const LossParams& p, int es, StreamCfg* c) {
   // warps per row: leave at least a third of the ring to loads in flight
   c->group = 1;
   while (c->group < 4 && kStreamWarps / c->group > (c->nslots * 2) / 3) c->group *= 2;
+  // a strip per row group for the raw values of the label positions that do not fit the register slots
+  const int gt = 32 * c->group, ngrp = kStreamWarps / c->group;
+  c->park_floats = (int)align_up((size_t)((p.Lmax + 1 > gt * kStreamGather) ? (p.Lmax + 1 - gt * kStreamGather) : 0), 4);
+  const int64_t park_bytes = (int64_t)ngrp * c->park_floats * 4;
+  while (c->nslots > 4 && (int64_t)c->nslots * c->slot_bytes + park_bytes > kStreamSmemBudget) --c->nslots;
+  if ((int64_t)c->nslots * c->slot_bytes + park_bytes > kStreamSmemBudget) return false;
+  c->smem = 2 * kStreamMaxSlots * (int)sizeof(uint64_t) + c->nslots * c->slot_bytes + (int)park_bytes;
   if (kStreamWarps / c->group > c->nslots - 1) return false;
   return true;
 }
@@ -425,7 +433,7 @@ static int launch_stream_t(const LossParams& p, const StreamCfg& c, cudaStream_t
   auto go = [&](auto kern) -> int {
     B200_CUDA(set_max_smem_cached((const void*)kern, c.smem));
     B200_CUDA(launch_kernel(kern, dim3((unsigned)g), dim3((kStreamWarps + 1) * 32), (size_t)c.smem, st,
-                            true, p, c.nslots, c.slot_bytes));
+                            true, p, c.nslots, c.slot_bytes, c.park_floats));
     return B200_OK;
   };
   if (c.group == 1) return go(ctc_stream_kernel<T, 1>);
