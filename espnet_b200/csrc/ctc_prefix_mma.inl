@@ -9,11 +9,14 @@
 // for the 1e-4 bar on log_psi, so both operands are split into a TF32 head and a TF32 tail and three products are
 // accumulated in fp32 (head*head + tail*head + head*tail; what is dropped is below 2^-21 relative per term).
 //
-// The rows of x arrive as in prefix_score_ring_kernel: one producer lane, 1-D bulk copies of 256-token rows into a
-// ring of 8-frame slots (rows padded to 264 floats: the B fragments of a warp then read 32 distinct banks).
+// The rows of x arrive as in prefix_score_ring_kernel: one producer lane, 1-D bulk copies of a tile's rows into a
+// ring of 8-frame slots (rows padded by 8 floats: the B fragments of a warp then read 32 distinct banks).
 namespace b200 {
 
-constexpr int kMmaTile = 256;          // tokens per CTA
+// tokens per CTA.  192 (three consumer warps) instead of 256: at C3 (V = 5000, 32 utterances) that is 864 CTAs of
+// 32 KB, six on most SMs and five on the rest, against 660 CTAs of 40 KB that put five on some SMs and four on
+// the others -- the SMs with the most CTAs set the kernel's time (C3 step: 150 -> 144.5 us; 128-token tiles: 146.4).
+constexpr int kMmaTile = 192;
 constexpr int kMmaWarpTok = 64;        // tokens per consumer warp (8 n-tiles)
 constexpr int kMmaNT = kMmaWarpTok / 8;
 constexpr int kMmaConsumers = (kMmaTile / kMmaWarpTok) * 32;
@@ -49,7 +52,7 @@ __device__ __forceinline__ void tf32_split(float v, uint32_t& head, uint32_t& ta
 }
 
 template <int DBG>
-__global__ void __launch_bounds__(kMmaConsumers + 32, 5) prefix_score_mma_kernel(ScoreParams p) {
+__global__ void __launch_bounds__(kMmaConsumers + 32, 7) prefix_score_mma_kernel(ScoreParams p) {
   extern __shared__ __align__(128) unsigned char mm_smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(mm_smem);  // [kMmaSlots]
   uint64_t* empty = full + kMmaSlots;                     // [kMmaSlots]
