@@ -20,7 +20,11 @@ constexpr int kClusterWarps = 8;                              // state warps per
 constexpr int kClusterThreads = kClusterWarps * 32;
 constexpr int kClusterMaxWarps = kClusterCtas * kClusterWarps;  // 32: L + 1 <= 1024
 constexpr int kClusterRing = 512;                               // boundary records per warp (frames)
-constexpr int kClusterSlack = 8;                                // chunks of slack in the level feedback (see `delay`)
+// Chunks of slack in the level feedback (see `delay`) and level records every kP-th chunk: 8 and 4 were 2 % faster at
+// C5 (1.05 vs 1.07 ms) but lengthen the horizon over which the level is PREDICTED ((delay + kP) x 8 frames), and on
+// tight lattices (T barely above what the labels need) the states then sit further from zero: gradient error 4.5e-5
+// against 1.1e-5 relative (the one-CTA kernel, 4-frame chunks: 0.7e-5; torch's float32 CTC on that input: 1e-3).
+constexpr int kClusterSlack = 0;
 
 __device__ __forceinline__ uint32_t cluster_rank() {
   uint32_t r;
@@ -123,8 +127,7 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
     // lane r < nca publishes this warp's level records into CTA r of the cluster
     const uint64_t wmx_dst = cluster_generic(cluster_map(smem_u32(s_wmx), (uint32_t)(lane < nca ? lane : 0))) + (uint64_t)gw * 8u;
     // The level record of chunk c - delay must be there when chunk c starts.  Successive warps run one chunk apart, so
-    // the last warp is nwa - 1 chunks (plus three hops between SMs) behind the first: with delay = nwa the first warp
-    // would wait for the last one at every second chunk and the whole ring of dependencies would set the pace.
+    // the last warp is nwa - 1 chunks (plus three hops between SMs) behind the first.
     const int delay = nwa + kClusterSlack;
 #ifdef B200_SWEEP_CLOCKS
     // developer instrumentation: SM clock at four points of chunks 64..127 for eight warps of the longest utterance
@@ -160,7 +163,7 @@ __global__ void __launch_bounds__(kClusterThreads) ctc_sweep_cluster_kernel(Loss
       outp += ostep;
     };
     auto chunk_begin = [&](int c, int n) -> float {
-      constexpr int kP = 4;  // (the one-CTA kernels: 2; here the per-chunk work sets the pace, see the header)
+      constexpr int kP = 2;
       if (c % kP) return 0.f;
       float corr = 0.f;
       const float wm = warp_max_redux(fmaxf(ab, al));

@@ -441,6 +441,25 @@ def test_many_utterances_more_ctas_than_sms():
         assert _normrel(grad, rg) <= TOL_F32
 
 
+@pytest.mark.parametrize("L", [260, 330])
+def test_many_long_utterances_more_clusters_than_sms(L):
+    """B = 48 utterances with L > 255: 48 x 2 clusters of 4 CTAs (384 CTAs) do not fit on 148 SMs at once, so the
+    cluster sweeps run in waves while the patch kernel (L = 260: warp per row; L = 330: CTA per row) is staged
+    behind them and follows the completion flags."""
+    c = _cases.make_loss_case(48, 2 * L + 30, 32, L, seed=78)
+    x, ilen, olen, ys = c["x"], c["ilen"], c["olen"], c["ys"]
+    for _ in range(2):
+        nll, grad, ls = _run(x, ilen, olen, ys)
+        rn, rg = _ref64(x, ilen, olen, ys)
+        np.testing.assert_allclose(nll, rn, rtol=TOL_F32)
+        np.testing.assert_allclose(ls, rn.sum(), rtol=TOL_F32)
+        # (tight lattices, ilen down to 0.6 T against up to 260 / 330 labels: bar as in the hand-over test below)
+        _, fg = _ref64(x, ilen, olen, ys, dt=torch.float32)
+        e_g, e_ref = _normrel(grad, rg), _normrel(fg, rg)
+        print(f"L={L}: grad error {e_g:.2e}, torch float32 {e_ref:.2e}")
+        assert e_g <= max(TOL_F32, e_ref), (e_g, e_ref)
+
+
 @pytest.mark.parametrize("split", [False, True])
 @pytest.mark.parametrize("Lmax", [255, 256, 257, 320, 321, 512, 513, 769, 1023])
 def test_long_label_sequences_at_the_kernel_boundaries(Lmax, split, sweep_domain):
