@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
         }
       }
 #pragma unroll
-      for (int x = 0; x < RR; ++x) m[x] = warp_max(m[x]);
+      for (int x = 0; x < RR; ++x) m[x] = warp_max_redux(m[x]);  // (REDUX.MAX on order-preserving ints: one instruction instead of five dependent shuffles)
 #pragma unroll
       for (int x = 0; x < RR; ++x) {
         w_all[x] = 0.f; w_blank[x] = 0.f;
@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
         logocc(st, k, ub, ul);
         m = fmaxf(m, fmaxf(ub, ul));
       }
-      m = warp_max(m);
+      m = warp_max_redux(m);
       for (int k = lane; k <= L; k += 32) {
         float ub, ul;
         logocc(st, k, ub, ul);

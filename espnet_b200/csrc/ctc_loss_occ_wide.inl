@@ -180,11 +180,11 @@ __global__ void __launch_bounds__(kWideThreads + 32) ctc_occ_wide_kernel(LossPar
           }
           m = fmaxf(m, fmaxf(ub[j], ul[j]));
         }
-        m = warp_max(m);
+        m = warp_max_redux(m);
         if (lane == 0) red[warp] = m;
         asm volatile("bar.sync 1, %0;" ::"n"(kWideThreads) : "memory");
         m = red[lane & (kWideWarps - 1)];
-        m = warp_max(m);
+        m = warp_max_redux(m);
         float w_all = 0.f, w_blank = 0.f;
 #pragma unroll
         for (int j = 0; j < kWideIter; ++j) {
