@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.environ.get("B200_CTC_LIB") or os.path.join(HERE, "libespnet_b200_ctc.so")
-SOURCES = ["api.cu", "ctc_loss.cu", "ctc_prefix.cu", "ctc_misc.cu", "peer.cu"]
+SOURCES = ["api.cu", "ctc_loss.cu", "ctc_prefix.cu", "ctc_misc.cu", "peer.cu", "beam_prune.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-shared", "-cudart", "static",

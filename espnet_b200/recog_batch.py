@@ -16,6 +16,7 @@ ended" and "may the search stop" are host decisions in the reference as well.
 import numpy as np
 import torch
 
+from . import _lib
 from .batch_beam_search import end_detect
 from .ctc_prefix_score import CTCPrefixScoreB200
 
@@ -42,16 +43,45 @@ class DecoderStep(object):
         raise NotImplementedError
 
 
+def beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, first_position):
+    """decoders.py:812-852 in ONE kernel (``b200_beam_prune``, csrc/beam_prune.cu): the joint local scores, the eos
+    scores, the accumulated scores and the per-utterance top-k over beam x V.
+
+    logp (batch*beam, V) fp32 log-softmax of the attention decoder; ctc_scores the same shape or None;
+    vscores (batch, beam).  Returns (best_scores (batch, beam), best_ids (batch, beam) in hyp * V + token space,
+    eos_vscores (batch, beam), tokens (batch*beam,), parent_rows (batch*beam,))."""
+    batch, beam = vscores.shape
+    V = logp.size(-1)
+    dev = logp.device
+    logp = logp.contiguous()
+    if ctc_scores is not None:
+        ctc_scores = ctc_scores.contiguous()
+    vscores = vscores.contiguous()
+    best_scores = torch.empty((batch, beam), dtype=torch.float32, device=dev)
+    eos_v = torch.empty((batch, beam), dtype=torch.float32, device=dev)
+    ids = torch.empty((3, batch, beam), dtype=torch.int64, device=dev)   # best_ids, tokens, parent rows
+    nb = batch * beam * 8
+    with torch.cuda.device(dev):
+        rc = _lib.load().b200_beam_prune(
+            logp.data_ptr(), None if ctc_scores is None else ctc_scores.data_ptr(), vscores.data_ptr(), batch, beam, V, beam,
+            float(att_weight), float(ctc_weight), int(eos), 1 if first_position else 0, best_scores.data_ptr(),
+            ids.data_ptr(), eos_v.data_ptr(), ids.data_ptr() + nb, ids.data_ptr() + 2 * nb,
+            torch.cuda.current_stream(dev).cuda_stream)
+    _lib.check(rc, "b200_beam_prune")
+    return best_scores, ids[0], eos_v, ids[1].view(-1), ids[2].view(-1)
+
+
 def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, maxlenratio=0.0, minlenratio=0.0,
                          penalty=0.0, nbest=1, ctc_margin=0, normalize_score=True, pre_beam=None, scorer=None,
-                         stats=None):
+                         stats=None, fused=True):
     """Batched joint CTC/attention beam search (decoders.py:641-974 with one encoder, no LM).
 
     decoder: a DecoderStep; lpz (batch, T, odim) CTC log-probs on the device (or None: attention only);
     hlens: per-utterance encoder lengths; pre_beam: None = the reference's rule (decoders.py:759-765: 1.5 x beam
     candidates from the attention scores on CPU inputs, all tokens on CUDA inputs -- here the inputs are always on
     CUDA, so None means all tokens), or the number of candidates.
-    stats: a dict that receives {"steps": output positions the loop ran}.
+    stats: a dict that receives {"steps": output positions the loop ran}.  fused=False: the score accumulation and the
+    top-k as eager torch operations (the reference's lines) instead of ``b200_beam_prune``.
     Returns the n-best list per utterance: [{"yseq": [...], "score": float}, ...] sorted by score.
     """
     hl = [int(v) for v in (hlens.tolist() if torch.is_tensor(hlens) else hlens)]
@@ -83,22 +113,32 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
         logp, att_w, state = decoder.step(vy, state)
         if odim is None:
             odim = logp.size(-1)
-        local = att_weight * logp
+        ctc_scores = None
         if scorer is not None:
-            local[:, 0] = LOGZERO  # avoid choosing blank (:816)
-            part_ids = torch.topk(local, scoring_num, dim=-1)[1] if scoring_num > 0 else None
+            part_ids = None
+            if scoring_num > 0:   # pre-beam on the attention scores with the blank masked (:816-822)
+                local = att_weight * logp
+                local[:, 0] = LOGZERO
+                part_ids = torch.topk(local, scoring_num, dim=-1)[1]
             ctc_scores, ctc_state = scorer(yseq[:, :i + 1], ctc_state, part_ids, att_w)
-            local = local + ctc_weight * ctc_scores
-        local = local.view(batch, beam, odim)
-        if i == 0:
-            local[:, 1:, :] = LOGZERO
-        # accumulate scores, global pruning (:840-846)
-        eos_v = local[:, :, eos] + vscores
-        acc = vscores.view(batch, beam, 1) + local
-        acc[:, :, eos] = LOGZERO
-        best_scores, best_ids = torch.topk(acc.view(batch, -1), beam, 1)
-        tok = torch.fmod(best_ids, odim).view(-1)
-        vidx = (torch.div(best_ids, odim, rounding_mode="floor") + pad_b).view(-1)
+        if fused and logp.dtype == torch.float32 and beam <= 128 and beam * odim < 2 ** 31:
+            # joint local scores, eos scores, accumulated scores and the per-utterance top-k in one kernel
+            best_scores, best_ids, eos_v, tok, vidx = beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, i == 0)
+        else:
+            local = att_weight * logp
+            if scorer is not None:
+                local[:, 0] = LOGZERO  # avoid choosing blank (:816)
+                local = local + ctc_weight * ctc_scores
+            local = local.view(batch, beam, odim)
+            if i == 0:
+                local[:, 1:, :] = LOGZERO
+            # accumulate scores, global pruning (:840-846)
+            eos_v = local[:, :, eos] + vscores
+            acc = vscores.view(batch, beam, 1) + local
+            acc[:, :, eos] = LOGZERO
+            best_scores, best_ids = torch.topk(acc.view(batch, -1), beam, 1)
+            tok = torch.fmod(best_ids, odim).view(-1)
+            vidx = (torch.div(best_ids, odim, rounding_mode="floor") + pad_b).view(-1)
         y_prev = yseq
         yseq = yseq.index_select(0, vidx)
         yseq[:, i + 1] = tok

@@ -182,6 +182,21 @@ int b200_ctc_stage_labels_pinned(const int64_t* targets_host, int64_t n_targets,
  * Process-wide; returns the previous setting. */
 int b200_ctc_debug_force_log_sweep(int on);
 
+/* Score accumulation and per-utterance top-k of one output position of the joint CTC/attention search loop.
+ * Replaces espnet/nets/pytorch_backend/rnn/decoders.py:812-852 (Decoder.recognize_beam_batch):
+ *   local = att_weight * att_logp;  [ctc_scores != NULL: local[:, 0] = -1e10; local += ctc_weight * ctc_scores;]
+ *   [first_position: local of hypotheses 1.. of every utterance = -1e10]
+ *   eos_vscores = local[:, eos] + vscores;  acc = vscores + local with the eos column at -1e10;
+ *   best_scores, best_ids = topk(acc per utterance over beam * V, k)   (sorted; ties in index order)
+ *   tokens = best_ids % V;  parent_rows = best_ids / V + utterance * beam.
+ * att_logp / ctc_scores: (batch*beam, V) fp32 contiguous device memory; vscores, eos_vscores: (batch, beam) fp32;
+ * best_scores (batch, k) fp32; best_ids / tokens / parent_rows (batch, k) int64.  1 <= k <= 128.  float32 operation
+ * order as in the eager formula (no FMA contraction): the values are the reference's bit for bit. */
+int b200_beam_prune(const float* att_logp, const float* ctc_scores, const float* vscores, int64_t batch,
+                    int64_t beam, int64_t V, int64_t k, float att_weight, float ctc_weight, int eos,
+                    int first_position, float* best_scores, int64_t* best_ids, float* eos_vscores,
+                    int64_t* tokens, int64_t* parent_rows, void* stream);
+
 /* Developer switch: on != 0 runs the lattice sweeps of utterances with 256 <= Lmax + 1 <= 1024 in one CTA per
  * (utterance, direction) instead of a 4-CTA thread-block cluster (A/B timing; the tests run both). */
 void b200_ctc_debug_single_cta_sweep(int on);

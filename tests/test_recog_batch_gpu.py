@@ -86,3 +86,60 @@ def test_attention_only_and_empty_results():
 
     out = recognize_beam_batch(Never(), None, [3, 2], 2, 5, 5, ctc_weight=0.0, nbest=2)
     assert len(out) == 2 and all(len(h) >= 1 for h in out)
+
+
+def _prune_eager(logp, ctc, vscores, eos, aw, cw, first):
+    """decoders.py:812-852 as eager torch operations."""
+    batch, beam = vscores.shape
+    V = logp.size(-1)
+    local = aw * logp
+    if ctc is not None:
+        local[:, 0] = -10000000000.0
+        local = local + cw * ctc
+    local = local.view(batch, beam, V)
+    if first:
+        local[:, 1:, :] = -10000000000.0
+    eos_v = local[:, :, eos] + vscores
+    acc = vscores.view(batch, beam, 1) + local
+    acc[:, :, eos] = -10000000000.0
+    s, ids = torch.topk(acc.view(batch, -1), beam, 1)
+    return s, ids, eos_v, acc.view(batch, -1)
+
+
+@pytest.mark.parametrize("batch,beam,V", [(3, 4, 50), (32, 10, 5000), (2, 60, 1000), (1, 1, 7), (5, 7, 33)])
+@pytest.mark.parametrize("with_ctc,first", [(True, False), (True, True), (False, False)])
+def test_beam_prune_kernel_equals_the_eager_formula(batch, beam, V, with_ctc, first):
+    """b200_beam_prune against the reference's own lines: scores bitwise (same float32 operation order), the selected
+    ids identical wherever the k-th value is not tied, eos scores bitwise, tokens / parent rows consistent."""
+    from espnet_b200.recog_batch import beam_prune
+
+    g = torch.Generator(device="cuda").manual_seed(1000 * batch + beam + V)
+    dev = torch.device("cuda")
+    logp = torch.log_softmax(torch.randn(batch * beam, V, generator=g, device=dev) * 3, dim=1)
+    ctc = (torch.randn(batch * beam, V, generator=g, device=dev) * 8 - 10) if with_ctc else None
+    if with_ctc:
+        ctc[:, V // 2] = -10000000000.0   # an unscored token, as the prefix scorer returns it
+    vs = torch.randn(batch, beam, generator=g, device=dev) * 5
+    eos = V - 1
+    s_ref, id_ref, eos_ref, acc = _prune_eager(logp.clone(), None if ctc is None else ctc.clone(), vs, eos, 0.7, 0.3, first)
+    s, ids, eos_v, tok, vidx = beam_prune(logp, ctc, vs, eos, 0.7, 0.3, first)
+    assert torch.equal(s, s_ref)                      # the same values, sorted
+    assert torch.equal(eos_v, eos_ref)
+    assert torch.equal(acc.gather(1, ids), s)         # every id holds the value reported for it
+    assert all(len(set(r)) == beam for r in ids.tolist())
+    untied = s_ref[:, -1] != torch.topk(acc, min(beam + 1, acc.size(1)), 1)[0][:, -1] if acc.size(1) > beam else None
+    strictly = (s_ref[:, 1:] != s_ref[:, :-1]).all(1) if beam > 1 else torch.ones(batch, dtype=torch.bool, device=dev)
+    rows = strictly if untied is None else (strictly & untied)
+    assert torch.equal(ids[rows], id_ref[rows])
+    assert torch.equal(tok.view(batch, beam), ids % V)
+    assert torch.equal(vidx.view(batch, beam), ids // V + torch.arange(batch, device=dev).view(-1, 1) * beam)
+
+
+def test_beam_prune_ties_are_taken_in_index_order():
+    from espnet_b200.recog_batch import beam_prune
+
+    dev = torch.device("cuda")
+    logp = torch.full((4, 10), -1.0, device=dev)      # batch 2 x beam 2, every candidate equal
+    vs = torch.zeros(2, 2, device=dev)
+    s, ids, _, _, _ = beam_prune(logp, None, vs, 9, 1.0, 0.0, False)
+    assert ids.tolist() == [[0, 1], [0, 1]] and (s == -1.0).all()
