@@ -12,8 +12,8 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "espnet_b200", "libespnet_b200_ctc.so")
-WANT = ["UBLKCP", "UTMALDG", "UTCMMA", "UTCHMMA", "LDTM", "SYNCS", "LDGSTS", "DFMA", "DMUL", "DADD", "MUFU", "REDUX",
-        "SHFL", "LDG", "STG", "LDS", "STS", "ATOM", "RED"]
+WANT = ["UBLKCP", "UTMALDG", "UTCMMA", "UTCHMMA", "LDTM", "HMMA", "SYNCS", "UCGABAR", "LDGSTS", "DFMA", "DMUL", "DADD", "MUFU",
+        "REDUX", "SHFL", "LDG", "STG", "LDS", "STS", "ATOM", "RED"]
 
 
 def main():
