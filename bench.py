@@ -776,13 +776,15 @@ def run_b200(args, rank, world, local_rank):
             decode_loop = [bench_decode_loop(dev), bench_decode_loop(dev, margin=40), bench_decode_loop(dev, pre_beam=15)]
         except Exception as e:  # a reported extra, never the reason the line is missing
             decode_loop = {"error": str(e)[:200]}
-    kernels = ["ctc_stream_kernel", "ctc_prep_kernel (under the stream kernel)", "ctc_sweep kernel (alpha+beta)",
+    kernels = ["ctc_label_fetch_kernel (labels from the pinned staging buffer)", "ctc_stream_kernel",
+               "ctc_prep_kernel (under the stream kernel)", "ctc_sweep kernel (alpha+beta)",
                "ctc_occ_kernel<PATCH>", "ctc_grad_rescale_kernel (backward: verifies the upstream scale)"]
     line = {"metric": "ctc_loss_fwd_bwd_utterances_per_sec", "value": value, "unit": "utterances/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16 logits, f32 lattice",
             "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e,
-            "gpu_launches": len(kernels) * args.steps, "kernels_per_step": kernels,
+            "gpu_launches": (len(kernels) + (1 if world > 1 else 0)) * args.steps,
+            "kernels_per_step": kernels + (["peer_sum_exchange_kernel (N > 1)"] if world > 1 else []),
             "host_issue_us_per_step": 1e6 * host_issue_s / args.steps, "cpu_affinity": affinity,
             "roofline": roofline, "roofline_step": roofline_step, "raw_abi": raw_abi,
             "cpu_baseline": cpu, "cpu_reference_c1": cpu_c1, "reference_gpu": ref_gpu, "loss": loss_value,
