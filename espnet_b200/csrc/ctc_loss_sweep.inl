@@ -723,12 +723,19 @@ static int launch_sweep_t(const LossParams& p, int threads, cudaStream_t st, boo
   return B200_OK;
 }
 
+constexpr size_t kSweepPadBytes = 114 * 1024;
+
 static int launch_sweep_staged(const LossParams& p, int threads, cudaStream_t st, bool pdl) {
   size_t smem = sweep_smem_bytes<256>(threads / 32) + sizeof(Tagged) * 2 * kCtlRing +
                 (size_t)kLpSlots * 8 * (p.ws.Kp + 1) * sizeof(float) + kLpSlots * sizeof(uint64_t);
   threads += 32;  // the helper warp
-  // one latency chain per SM whenever the grid fits that way (see launch_sweep_t)
-  if (2 * (p.b1 - p.b0) <= num_sms() && smem < 116 * 1024) smem = 116 * 1024;
+  // One latency chain per SM whenever the grid fits that way (see launch_sweep_t): 114 KB is more than half of an SM's
+  // shared memory (two sweep CTAs cannot share an SM) and leaves room for ONE CTA of the patch kernel (111.9 KB + the
+  // 1 KB the system reserves per CTA: 233344 of 233472 bytes) next to a running sweep CTA, so the patch kernel works
+  // through the utterances that have finished on ALL SMs, not only on the 20 without a sweep CTA.  (Measured at C2:
+  // 189.2 against 190.7 us per step with a 116 KB pad -- the patch warps that share an SM also take issue slots from
+  // the sweep's latency chain, so most of what they gain the sweep loses.)
+  if (2 * (p.b1 - p.b0) <= num_sms() && smem < kSweepPadBytes) smem = kSweepPadBytes;
   auto kern = ctc_sweep_staged_kernel;
   if (smem > 48 * 1024) B200_CUDA(set_max_smem_cached((const void*)kern, (int)smem));
   B200_CUDA(launch_kernel(kern, dim3((unsigned)(p.b1 - p.b0), 2), dim3(threads), smem, st, pdl, p));
