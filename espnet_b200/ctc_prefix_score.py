@@ -131,8 +131,9 @@ class CTCPrefixScoreB200(object):
         # frame window from the attention weights (ctc_prefix_score.py:145-154)
         if att_w is not None and self.margin > 0:
             f_arg = torch.matmul(att_w.to(torch.float32), self.frame_ids)
-            f_min = max(int(f_arg.min().cpu()), f_min_prev)
-            f_max = max(int(f_arg.max().cpu()), f_max_prev)
+            lo, hi = torch.stack(torch.aminmax(f_arg)).tolist()   # ONE device->host copy (the reference: two)
+            f_min = max(int(lo), f_min_prev)
+            f_max = max(int(hi), f_max_prev)
             start = min(f_max_prev, max(f_min - self.margin, output_length, 1))
             end = min(f_max + self.margin, T)
         else:
