@@ -4,6 +4,35 @@
 
 #include <mutex>
 
+// Developer instrumentation (-DB200_TIMELINE): global-timer stamps of the kernels of one call -- even slots keep the
+// minimum (first CTA / warp to get there), odd slots the maximum; slots 64 + 2*b + d: end of the sweep of utterance b,
+// direction d.  Read back / reset with b200_debug_timeline (tools/dev_timeline.py).
+#ifdef B200_TIMELINE
+namespace b200 {
+__device__ unsigned long long g_tl[1024];
+__device__ __forceinline__ unsigned long long tl_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+}  // namespace b200
+#define TL_MIN(i) atomicMin(&b200::g_tl[i], b200::tl_now())
+#define TL_MAX(i) atomicMax(&b200::g_tl[i], b200::tl_now())
+#define TL_SET(i) (b200::g_tl[i] = b200::tl_now())
+extern "C" int b200_debug_timeline(unsigned long long* host, int reset) {
+  if (reset) {
+    unsigned long long init[1024];
+    for (int i = 0; i < 1024; ++i) init[i] = (i < 64 && !(i & 1)) ? ~0ull : 0ull;
+    return (int)cudaMemcpyToSymbol(b200::g_tl, init, sizeof(init));
+  }
+  return (int)cudaMemcpyFromSymbol(host, b200::g_tl, sizeof(unsigned long long) * 1024);
+}
+#else
+#define TL_MIN(i) ((void)0)
+#define TL_MAX(i) ((void)0)
+#define TL_SET(i) ((void)0)
+#endif
+
 namespace b200 {
 
 // ============================================================================

@@ -63,6 +63,9 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
     fence_proxy_async();
   }
   __syncwarp();
+  if (lane == 0) TL_MIN(6);
+  bool tl_first = true;
+  (void)tl_first;
   uint32_t phase = 0;  // bit s: parity of the next completion of stage s
   T* grad = reinterpret_cast<T*>(p.grad);
   const bool pairs = NJ > 0 && stages == kOccMaxStages;
@@ -366,6 +369,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
         mbar_wait(&bars[si], (phase >> si) & 1u);
         phase ^= 1u << si;
       }
+      if (tl_first && lane == 0) { TL_MIN(4); tl_first = false; }
       if (PATCH && poison) {
         // infeasible utterance: every gradient element of its frames is NaN (as torch)
         const T nanv = ElemTraits<T>::from_float(__int_as_float(0x7fc00000));
@@ -397,6 +401,7 @@ __global__ void __launch_bounds__(256) ctc_occ_kernel(LossParams p, int stages) 
     lin_flush();
   }
   }  // next ticket
+  if (lane == 0) TL_MAX(5);
   // this grid must not be seen as finished before the sweeps it ran under
   pdl_wait();
 }

@@ -151,6 +151,7 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
   }
   __syncthreads();
   pdl_wait();  // (launched as a programmatic dependent of whatever precedes it on the stream: labels, logits)
+  if (threadIdx.x == 0) TL_MIN(0);
   // This kernel reads the caller's int64 labels itself (clamped exactly as the prep kernel clamps them), so
   // it does not wait for the prep kernel: prep is launched AFTER it as a programmatic dependent and runs
   // on the free thread slots of the SMs while the rows stream.
@@ -395,6 +396,7 @@ __global__ void __launch_bounds__((kStreamWarps + 1) * 32, 1) ctc_stream_kernel(
     }
   }
   if (gtid == 0) bulk_wait_all<0>();
+  if (gtid == 0) TL_MAX(1);
 }
 
 struct StreamCfg {

@@ -400,6 +400,7 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
     fence_proxy_async();
   }
   pdl_wait();
+  if (threadIdx.x == 0) TL_MIN(2);
   // the occupancy kernel may be staged from here on: it starts after EVERY sweep CTA has passed the wait above,
   // i.e. with prep complete (its counters zeroed), and follows the per-utterance completion flags
   pdl_launch_dependents();
@@ -701,6 +702,8 @@ __global__ void __launch_bounds__(288) ctc_sweep_staged_kernel(LossParams p) {
     // barrier above): the occupancy kernel may read it once both directions have signalled
     __threadfence();
     atomicAdd(p.ws.done + b, 1);
+    TL_MAX(3);
+    TL_SET(64 + 2 * b + d);
   }
 }
 
