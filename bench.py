@@ -445,6 +445,8 @@ def bench_prefix(dev, peak, steps=20, snum=0):
         y = [y[parents[i][k]] + [toks[i][k]] for k in range(B * H)]
     y_dev = [torch.tensor(yi, dtype=torch.int64, device=dev) for yi in ys]
 
+    host_us = []
+
     def walk(make_impl, do_step, do_select, n):
         impl = make_impl()
         state = None
@@ -453,9 +455,11 @@ def bench_prefix(dev, peak, steps=20, snum=0):
             if i == 2:  # steps 0 and 1 (warm-up: first label, first step with a previous state) are not timed
                 torch.cuda.synchronize()
                 e0.record()
+                h0 = time.perf_counter()
             st = do_step(impl, i, state)
             state = do_select(impl, st, best[i])
         e1.record()
+        host_us.append((time.perf_counter() - h0) * 1e6 / n)   # time the host needed to ISSUE a step
         torch.cuda.synchronize()
         return n / (e0.elapsed_time(e1) * 1e-3)
 
@@ -471,10 +475,27 @@ def bench_prefix(dev, peak, steps=20, snum=0):
            "config": {"workload": "C3: B=32 utterances x beam 10 (n_bh=320), T=500, V=5000, fp32 log-probs, "
                                   + ("scoring_ids=top-15 (pre-beam)" if snum else "scoring_ids=None") + ", margin=0",
                       "steps": steps},
-           "algorithmic_bytes_per_step": alg,
+           "algorithmic_bytes_per_step": alg, "host_issue_us_per_step": host_us[0],
            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
                         "frac_of_nominal_8TBs": gbs / NOMINAL_HBM_GBS,
                         "what": "whole step (all kernels of __call__ + index_select_state) against its algorithmic bytes"}}
+    if snum:
+        # the candidates' sums read a (B, V, T) column copy of x that the scorer builds at its first call with
+        # scoring_ids (inside the untimed first step, once per batch of utterances): its cost, and the step without it
+        plain = walk(lambda: CTCPrefixScoreB200(lp.clone(), xlens, 0, eos, columns=False),
+                     lambda m, i, s: m(y_dev[i], s, ids_dev[i])[1], lambda m, st, b: m.index_select_state(st, b), steps)
+        m = CTCPrefixScoreB200(lp.clone(), xlens, 0, eos)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        m._column_copy()
+        e1.record()
+        torch.cuda.synchronize()
+        out["column_copy"] = {"one_time_us": e0.elapsed_time(e1) * 1e3, "bytes": 2 * 4 * B * T_ * V_,
+                              "us_per_step_without_it": 1e6 / plain,
+                              "what": "x (B,T,V) -> (B,V,T) once per batch of utterances, so that a candidate's frames are "
+                                      "contiguous (b200_ctc_prefix_columns / b200_ctc_prefix_score_columns)"}
+        del m
     ref_kind = None
     try:
         from oracle import stage_ref

@@ -32,6 +32,10 @@ SIGNATURES = {
     "b200_ctc_prefix_work_floats": (_sz, [_i64, _i64, _i64]),
     "b200_ctc_prefix_score": (_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _int, _int, _vp, _vp,
                                      _vp, _i64, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "b200_ctc_prefix_column_stride": (_i64, [_i64]),
+    "b200_ctc_prefix_columns": (_int, [_vp, _i64, _i64, _i64, _vp, _vp]),
+    "b200_ctc_prefix_score_columns": (_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _int, _int, _vp, _vp,
+                                             _vp, _i64, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
     "b200_ctc_prefix_select": (_int, [_vp, _i64, _i64, _i64, _i64, _int, _vp, _vp, _vp, _i64,
                                       _i64, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "b200_ctc_debug_force_log_sweep": (_int, [_int]),

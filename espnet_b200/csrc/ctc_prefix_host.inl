@@ -80,11 +80,23 @@ static void launch_full(const ScoreParams& p, cudaStream_t st) {
   prefix_score_last_kernel<<<(unsigned)((p.n_bh + 3) / 4), 128, 0, st>>>(p);
 }
 
-extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const int64_t* xlens, int64_t B, int64_t T,
-                                     int64_t V, int64_t n_hyps, int blank, int eos, const float* r_prev,
-                                     const float* s_prev, const int64_t* last_ids, int64_t output_len,
-                                     const int64_t* scoring_ids, int64_t snum, int64_t start, int64_t end,
-                                     float* scores, float* log_psi, float* work, void* stream) {
+extern "C" int64_t b200_ctc_prefix_column_stride(int64_t T) { return T < 1 ? 0 : (T + 31) & ~(int64_t)31; }
+
+extern "C" int b200_ctc_prefix_columns(const float* x, int64_t B, int64_t T, int64_t V, float* x_cols, void* stream) {
+  B200_CHECK_ARG(x && x_cols, B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(B >= 1 && T >= 1 && V >= 2 && B < 65536 && (T + 31) / 32 < 65536, B200_ERR_INVALID_ARGUMENT,
+                 "need 1<=B<65536, 1<=T<2^21, V>=2, got B=%lld T=%lld V=%lld", (long long)B, (long long)T, (long long)V);
+  dim3 grid((unsigned)((V + 31) / 32), (unsigned)((T + 31) / 32), (unsigned)B);
+  prefix_columns_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, (int)T, (int)V, (int)b200_ctc_prefix_column_stride(T), x_cols);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+static int prefix_score_impl(const float* x, const float* x_cols, const float* xmax, const int64_t* xlens, int64_t B, int64_t T,
+                             int64_t V, int64_t n_hyps, int blank, int eos, const float* r_prev,
+                             const float* s_prev, const int64_t* last_ids, int64_t output_len,
+                             const int64_t* scoring_ids, int64_t snum, int64_t start, int64_t end,
+                             float* scores, float* log_psi, float* work, void* stream) {
   int rc = check_prefix(B, T, V, n_hyps, blank, start, end);
   if (rc) return rc;
   B200_CHECK_ARG(x && xmax && xlens && r_prev && last_ids && scores && log_psi && work,
@@ -102,6 +114,17 @@ extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const in
   p.scoring_ids = scoring_ids; p.snum = (int)snum;
   p.scores = scores; p.log_psi = log_psi;
   p.w = carve_prefix(work, B, T, n_hyps);
+  p.xc = x_cols; p.Tc = (int)b200_ctc_prefix_column_stride(T);
+  if (snum > 0 && x_cols) {
+    // candidates from the column copy: phi, fill, sums and the exact redo in one kernel, a CTA per hypothesis
+    const size_t smem = sizeof(float) * 4 * (size_t)(end > start ? end - start : 0);
+    if (smem <= 200u * 1024u &&
+        (smem <= 40u * 1024u || set_max_smem_cached((const void*)prefix_score_cols_kernel, (int)smem) == cudaSuccess)) {
+      prefix_score_cols_kernel<<<p.n_bh, kColsThreads, smem, st>>>(p, xlens);
+      B200_CUDA(cudaGetLastError());
+      return B200_OK;
+    }
+  }
   prefix_phi_kernel<<<p.n_bh, 128, 0, st>>>(r_prev, xlens, (int)T, (int)n_hyps, p.n_bh, p.start, p.end, p.w);
   B200_CUDA(cudaGetLastError());
   p.hyp_off = 0;
@@ -132,6 +155,24 @@ extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const in
   prefix_score_fix_kernel<<<2 * num_sms(), 256, 0, st>>>(p);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
+}
+
+extern "C" int b200_ctc_prefix_score(const float* x, const float* xmax, const int64_t* xlens, int64_t B, int64_t T,
+                                     int64_t V, int64_t n_hyps, int blank, int eos, const float* r_prev,
+                                     const float* s_prev, const int64_t* last_ids, int64_t output_len,
+                                     const int64_t* scoring_ids, int64_t snum, int64_t start, int64_t end,
+                                     float* scores, float* log_psi, float* work, void* stream) {
+  return prefix_score_impl(x, nullptr, xmax, xlens, B, T, V, n_hyps, blank, eos, r_prev, s_prev, last_ids, output_len,
+                           scoring_ids, snum, start, end, scores, log_psi, work, stream);
+}
+
+extern "C" int b200_ctc_prefix_score_columns(const float* x, const float* x_cols, const float* xmax, const int64_t* xlens,
+                                             int64_t B, int64_t T, int64_t V, int64_t n_hyps, int blank, int eos,
+                                             const float* r_prev, const float* s_prev, const int64_t* last_ids,
+                                             int64_t output_len, const int64_t* scoring_ids, int64_t snum, int64_t start,
+                                             int64_t end, float* scores, float* log_psi, float* work, void* stream) {
+  return prefix_score_impl(x, x_cols, xmax, xlens, B, T, V, n_hyps, blank, eos, r_prev, s_prev, last_ids, output_len,
+                           scoring_ids, snum, start, end, scores, log_psi, work, stream);
 }
 
 extern "C" int b200_ctc_prefix_select(const float* x, int64_t B, int64_t T, int64_t V, int64_t n_hyps, int blank,

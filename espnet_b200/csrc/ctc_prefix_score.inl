@@ -19,6 +19,8 @@ struct ScoreParams {
   float* log_psi;  // (n_bh,V)
   PrefixWork w;
   int hyp_off;     // the full-vocabulary kernels handle hypotheses [hyp_off, hyp_off + NH) of every utterance
+  const float* xc; // (B,V,Tc) column copy of x (b200_ctc_prefix_columns) or null
+  int Tc;
 };
 
 // The scaled linear sum loses every term below 2^-126 of the largest representable one (flush to zero).
@@ -517,6 +519,126 @@ __global__ void __launch_bounds__(256) prefix_score_partial_kernel(ScoreParams p
     p.log_psi[(int64_t)h * p.V + c] = psi;
     p.scores[(int64_t)h * p.V + c] = psi - sp;
   }
+}
+
+// The candidate (pre-beam) step from the column copy of x (b200_ctc_prefix_columns: (B,V,Tc), a token's frames
+// contiguous), ONE kernel.  The kernels above gather one 4-byte word per frame from rows V floats apart: every word
+// costs a DRAM sector of its own (x is larger than L2 at C3: 34 us for 4800 pairs), and the step is four launches (phi,
+// fill, partial, fix) that the host cannot issue as fast as the GPU runs them.  Here a CTA owns a hypothesis: it computes
+// the hypothesis' phi and E columns into shared memory (what prefix_phi_kernel writes to the workspace), fills its score
+// rows (prefix_fill_kernel), and each warp takes candidates -- 128-byte coalesced reads of the token's column, the same
+// accumulation order as prefix_score_partial_kernel, and a sum that underflowed is redone in log space by the same
+// warp on the spot (prefix_score_fix_kernel's arithmetic), so the results are the four-kernel path's bit for bit.
+constexpr int kColsThreads = 512;
+__global__ void __launch_bounds__(kColsThreads) prefix_score_cols_kernel(ScoreParams p, const int64_t* __restrict__ xlens) {
+  extern __shared__ float s_e[];  // [4][n]: phi_a, phi_b (log), EA, EB of this hypothesis for frames start-1 .. end-2
+  __shared__ float s_red[2][kColsThreads / 32];
+  __shared__ float s_rend;
+  const int h = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int u = h / p.n_hyps;
+  const int n = p.end > p.start ? p.end - p.start : 0;
+  float* s_pa = s_e;
+  float* s_pb = s_e + n;
+  float* s_ea = s_e + 2 * n;
+  float* s_eb = s_e + 3 * n;
+  float ma = -3.0e38f, mb = -3.0e38f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int t = p.start - 1 + i;
+    const float rn = p.r_prev[((int64_t)t * 2 + 0) * p.n_bh + h];
+    const float rb = p.r_prev[((int64_t)t * 2 + 1) * p.n_bh + h];
+    const float pa = lse2_nat(rn, rb);
+    s_pa[i] = pa;
+    s_pb[i] = rb;
+    ma = fmaxf(ma, pa);
+    mb = fmaxf(mb, rb);
+  }
+  ma = warp_max(ma);
+  mb = warp_max(mb);
+  if (lane == 0) { s_red[0][warp] = ma; s_red[1][warp] = mb; }
+  if (threadIdx.x == 0) {
+    const int te = (int)xlens[u] - 1;
+    s_rend = lse2_nat(p.r_prev[((int64_t)te * 2 + 0) * p.n_bh + h], p.r_prev[((int64_t)te * 2 + 1) * p.n_bh + h]);
+  }
+  __syncthreads();
+  ma = warp_max(lane < nw ? s_red[0][lane] : -3.0e38f);
+  mb = warp_max(lane < nw ? s_red[1][lane] : -3.0e38f);
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    s_ea[i] = ex2f((s_pa[i] - ma) * B200_LOG2E);
+    s_eb[i] = ex2f((s_pb[i] - mb) * B200_LOG2E);
+  }
+  const float sp = p.s_prev ? p.s_prev[h] : 0.f;
+  {
+    // rows of the hypothesis: logzero everywhere, r_sum[xlen-1] at eos (ctc_prefix_score.py:182-186)
+    float* lrow = p.log_psi + (int64_t)h * p.V;
+    float* srow = p.scores + (int64_t)h * p.V;
+    const float rend = s_rend;
+    for (int c = threadIdx.x; c < p.V; c += blockDim.x) {
+      const float psi = (c == p.eos && c != p.blank) ? rend : B200_LZ;
+      lrow[c] = psi;
+      srow[c] = psi - sp;
+    }
+  }
+  __syncthreads();  // E complete; the fill precedes the candidates' stores
+  const int64_t last = p.last_ids[h];
+  for (int q = warp; q < p.snum; q += nw) {
+    const int64_t c64 = p.scoring_ids[(int64_t)h * p.snum + q];
+    if (c64 < 0 || c64 >= p.V || c64 == p.blank || c64 == p.eos) continue;  // filled already
+    const int c = (int)c64;
+    const bool is_last = (c64 == last);
+    const float* col = p.xc + ((int64_t)u * p.V + c) * p.Tc;
+    const float* e = (is_last ? s_eb : s_ea) - p.start;  // e[t] = E[t-1]
+    const float mx = p.xmax[(int64_t)u * p.V + c];
+    const float mxl = mx * B200_LOG2E;
+    float a0 = 0.f, a1 = 0.f;
+    int t = p.start + lane;
+#pragma unroll 4
+    for (; t + 32 < p.end; t += 64) {
+      const float x0 = ld_nc_f32(col + t), x1 = ld_nc_f32(col + t + 32);
+      a0 = fmaf(e[t], ex2f(fmaf(x0, B200_LOG2E, -mxl)), a0);
+      a1 = fmaf(e[t + 32], ex2f(fmaf(x1, B200_LOG2E, -mxl)), a1);
+    }
+    if (t < p.end) a0 = fmaf(e[t], ex2f(fmaf(ld_nc_f32(col + t), B200_LOG2E, -mxl)), a0);
+    const float a = __shfl_sync(0xffffffffu, warp_sum(a0 + a1), 0);  // (one value for the whole warp: the branch below is collective)
+    const float x0 = (p.output_len == 0) ? col[0] : B200_LZ;
+    float psi;
+    if (a < kScoreAccFloor && n > 0) {
+      // the scaled sum underflowed: logsumexp over { phi[t-1] + x[t,c] } as written (ctc_prefix_score.py:165-180)
+      const float* ph = (is_last ? s_pb : s_pa) - p.start;
+      float m = -3.0e38f, sacc = 0.f;
+      for (int tt = p.start + lane; tt < p.end; tt += 32) {
+        const float v = ph[tt] + ld_nc_f32(col + tt);
+        const float mn = fmaxf(m, v);
+        sacc = sacc * ex2f((m - mn) * B200_LOG2E) + ex2f((v - mn) * B200_LOG2E);
+        m = mn;
+      }
+      const float mw = warp_max(m);
+      sacc = warp_sum(sacc * ex2f((m - mw) * B200_LOG2E));
+      psi = sacc > 0.f ? mw + B200_LN2 * lg2f(sacc) : B200_LZ;
+      psi = fmaxf(psi, B200_LZ);
+      if (x0 > B200_LZ) psi = lse2_nat(psi, x0);
+    } else {
+      psi = finish_psi(a, (is_last ? mb : ma) + mx, x0);
+    }
+    if (lane == 0) {
+      p.log_psi[(int64_t)h * p.V + c] = psi;
+      p.scores[(int64_t)h * p.V + c] = psi - sp;
+    }
+  }
+}
+
+// x (B,T,V) -> xc (B,V,Tc): 32 x 32 tiles through shared memory, reads coalesced along V, writes along T.
+__global__ void __launch_bounds__(256) prefix_columns_kernel(const float* __restrict__ x, int T, int V, int Tc,
+                                                             float* __restrict__ xc) {
+  __shared__ float tile[32][33];
+  const int u = blockIdx.z, v0 = blockIdx.x * 32, t0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const float* xu = x + (int64_t)u * T * V;
+  float* cu = xc + (int64_t)u * V * Tc;
+  for (int i = ty; i < 32; i += 8)
+    if (t0 + i < T && v0 + tx < V) tile[i][tx] = xu[(int64_t)(t0 + i) * V + v0 + tx];
+  __syncthreads();
+  for (int i = ty; i < 32; i += 8)
+    if (v0 + i < V && t0 + tx < T) cu[(int64_t)(v0 + i) * Tc + t0 + tx] = tile[tx][i];
 }
 
 // Exact log-space redo of the queued (hypothesis, token) pairs (ctc_prefix_score.py:165-180 as written:

@@ -61,12 +61,17 @@ def beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, first_pos
     eos_v = torch.empty((batch, beam), dtype=torch.float32, device=dev)
     ids = torch.empty((3, batch, beam), dtype=torch.int64, device=dev)   # best_ids, tokens, parent rows
     nb = batch * beam * 8
-    with torch.cuda.device(dev):
-        rc = _lib.load().b200_beam_prune(
-            logp.data_ptr(), None if ctc_scores is None else ctc_scores.data_ptr(), vscores.data_ptr(), batch, beam, V, beam,
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    args = (logp.data_ptr(), None if ctc_scores is None else ctc_scores.data_ptr(), vscores.data_ptr(), batch, beam, V, beam,
             float(att_weight), float(ctc_weight), int(eos), 1 if first_position else 0, best_scores.data_ptr(),
             ids.data_ptr(), eos_v.data_ptr(), ids.data_ptr() + nb, ids.data_ptr() + 2 * nb,
-            torch.cuda.current_stream(dev).cuda_stream)
+            torch._C._cuda_getCurrentRawStream(idx))
+    fn = _lib.load().b200_beam_prune
+    if torch.cuda.current_device() == idx:   # (the device guard only where the current device is another)
+        rc = fn(*args)
+    else:
+        with torch.cuda.device(dev):
+            rc = fn(*args)
     _lib.check(rc, "b200_beam_prune")
     return best_scores, ids[0], eos_v, ids[1].view(-1), ids[2].view(-1)
 

@@ -272,6 +272,25 @@ int b200_ctc_prefix_score(const float* x, const float* xmax, const int64_t* xlen
                           int64_t start, int64_t end,
                           float* scores, float* log_psi, float* work, void* stream);
 
+/* The candidate (pre-beam) path from a column copy of x.  With scoring_ids the step reads, per
+ * (hypothesis, candidate), one word per frame from rows V floats apart (ctc_prefix_score.py:159-163
+ * gathers the same elements with index_select): one DRAM sector per word.
+ * b200_ctc_prefix_columns writes x_cols (B, V, Tc), Tc = b200_ctc_prefix_column_stride(T), once per
+ * batch of utterances AFTER b200_ctc_prefix_init (it must see the padded x);
+ * b200_ctc_prefix_score_columns is b200_ctc_prefix_score with that copy: same arguments, same results
+ * bit for bit, the candidates' sums read contiguous columns.  x_cols == NULL or snum == 0: exactly
+ * b200_ctc_prefix_score. */
+int64_t b200_ctc_prefix_column_stride(int64_t T);
+int b200_ctc_prefix_columns(const float* x, int64_t B, int64_t T, int64_t V, float* x_cols, void* stream);
+int b200_ctc_prefix_score_columns(const float* x, const float* x_cols, const float* xmax,
+                                  const int64_t* xlens, int64_t B, int64_t T, int64_t V,
+                                  int64_t n_hyps, int blank, int eos,
+                                  const float* r_prev, const float* s_prev,
+                                  const int64_t* last_ids, int64_t output_len,
+                                  const int64_t* scoring_ids, int64_t snum,
+                                  int64_t start, int64_t end,
+                                  float* scores, float* log_psi, float* work, void* stream);
+
 /* Forward variables of the survivors: for new hypothesis k (0..n_new) with
  * parent hypothesis parent[k] (index into the n_bh prefixes of the step that
  * produced `work`) and appended token token[k]:

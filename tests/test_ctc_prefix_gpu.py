@@ -200,3 +200,68 @@ def test_scorer_adapter_batch_and_single_paths_agree():
     sa2, _ = a.batch_score_partial(y2, ids2, [ha], x)
     sb2, _ = b.score_partial(y2[0], ids2[0], hb, x)
     np.testing.assert_allclose(sa2[0, ids2[0]].cpu().numpy(), sb2.cpu().numpy(), atol=1e-5)
+
+
+@pytest.mark.parametrize("T,V,H,snum,margin,kind", [(203, 517, 10, 15, 0, "randn"), (64, 40, 3, 39, 0, "randn"),
+                                                    (333, 1000, 20, 60, 20, "randn"), (31, 33, 1, 1, 0, "randn"),
+                                                    (203, 517, 10, 15, 0, "scale30"), (150, 300, 5, 40, 15, "trained")])
+def test_candidate_path_from_column_copy_is_bit_identical(T, V, H, snum, margin, kind):
+    """scoring_ids with and without the (B, V, T) column copy of x: the same bits, step after step -- ragged lengths,
+    T not a multiple of the copy's 32-frame tiles, an attention window, candidates that repeat the last label and
+    blank / eos / -1 entries (which the fill kernel has already answered), saturated posteriors (pairs whose scaled sum
+    underflows and is redone in log space: by the fix kernel on one side, by the scoring warp itself on the other)."""
+    from espnet_b200.ctc_prefix_score import CTCPrefixScoreB200
+
+    c = _cases.make_prefix_case(3, T, V, H, seed=4242 + T, nsteps=4, kind=kind)
+    lp, xlens, eos = c["lp"], c["xlens"], c["eos"]
+    B = lp.size(0)
+    g = torch.Generator().manual_seed(T)
+    a = CTCPrefixScoreB200(lp.clone().cuda(), xlens, 0, eos, margin=margin, columns=True)
+    b = CTCPrefixScoreB200(lp.clone().cuda(), xlens, 0, eos, margin=margin, columns=False)
+    y = torch.full((B * H, 1), eos, dtype=torch.int64, device="cuda")
+    sa = sb = None
+    fixes = 0
+    for step in range(4):
+        ids = torch.stack([torch.randperm(V - 1, generator=g)[:snum] + 1 for _ in range(B * H)])
+        ids[:, 0] = y[:, -1].cpu()                       # the repeated last label is always a candidate
+        if snum > 3:
+            ids[0, 1], ids[1, 2], ids[2, 3] = 0, eos, -1
+        att_w = None
+        if margin:
+            centre = min(T - 1, 8 + 12 * step)
+            att_w = torch.zeros(B * H, T)
+            att_w[:, centre] = 1.0
+            att_w = att_w.cuda()
+        ga, sta = a(y, sa, ids.cuda(), att_w)
+        gb, stb = b(y, sb, ids.cuda(), att_w)
+        assert a._xc is not None and b._xc is None
+        # (the queue counter of the four-kernel path: csrc/ctc_prefix.cu carve_prefix)
+        fixes += int(b._work.view(torch.int32)[2 * B * T * ((H + 3) & ~3) + 3 * B * H])
+        assert torch.equal(ga, gb)
+        assert torch.equal(sta[1], stb[1])              # log_psi
+        hyp = torch.randint(0, H, (B, H), generator=g)
+        pick = torch.randint(0, snum, (B, H), generator=g)
+        tok = ids.clamp(min=1).view(B, H, snum)[torch.arange(B).view(-1, 1), hyp, pick]
+        tok = torch.where(tok == eos, torch.ones_like(tok), tok)
+        best = (hyp * V + tok).cuda()
+        sa = a.index_select_state(sta, best)
+        sb = b.index_select_state(stb, best)
+        assert torch.equal(sa[0], sb[0]) and torch.equal(sa[1], sb[1])
+        parent = (hyp + torch.arange(B).view(-1, 1) * H).view(-1).cuda()
+        y = torch.cat([y[parent], tok.view(-1, 1).cuda()], dim=1)
+    if kind == "scale30":
+        assert fixes > 0   # the log-space redo was exercised
+
+
+def test_column_copy_is_the_transpose():
+    from espnet_b200 import _lib
+
+    lib = _lib.load()
+    B, T, V = 2, 77, 101
+    x = torch.randn(B, T, V, device="cuda")
+    tc = lib.b200_ctc_prefix_column_stride(T)
+    assert tc == 96
+    xc = torch.full((B, V, tc), float("nan"), device="cuda")
+    _lib.check(lib.b200_ctc_prefix_columns(x.data_ptr(), B, T, V, xc.data_ptr(), torch.cuda.current_stream().cuda_stream), "columns")
+    assert torch.equal(xc[:, :, :T], x.transpose(1, 2))
+    assert torch.isnan(xc[:, :, T:]).all()              # the pad is never written (and never read)

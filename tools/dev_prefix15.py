@@ -8,4 +8,4 @@ if len(sys.argv) > 3:
     from espnet_b200 import _lib
     _lib.load().b200_ctc_debug_prefix_fp32_score({"fp32": 1, "copies": 2}[sys.argv[3]])
 out = bench.bench_prefix(torch.device("cuda", 0), 6459.3, steps=int(sys.argv[1]) if len(sys.argv) > 1 else 6, snum=int(sys.argv[2]) if len(sys.argv) > 2 else 15)
-print(out["value"], out["us_per_step"])
+print(out["value"], out["us_per_step"], "host", out["host_issue_us_per_step"], out.get("column_copy"))
