@@ -7,16 +7,20 @@
 //     eos_vscores = local[:, :, eos] + vscores             (:841)
 //     vscores = vscores + local, with the eos column at logzero; topk(beam) per utterance   (:842-846)
 // i.e. ~10 elementwise launches over (batch*beam, V) and torch.topk over rows of beam*V floats (a multi-pass radix
-// select of its own: ~76 us for 32 x 50 000 on a B200) -- here ONE kernel, one CTA per utterance: the values are
+// select of its own: ~76 us for 32 x 50 000 on a B200) -- here ONE kernel, one 4-CTA cluster per utterance: the values are
 // recomputed from the two score matrices on every pass (they stay in L2) with the reference's float32 operation
 // order (mul, mul, add, add: no FMA contraction, so the values and therefore the selected set are those of the
 // eager formula), the k-th largest value is found by a 4 x 8-bit radix select on order-preserving integer keys,
 // ties at the threshold are taken in index order, and the k winners leave sorted (value descending, index ascending).
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace b200 {
+namespace cg = cooperative_groups;
 
 constexpr int kPruneThreads = 1024;
+constexpr int kPruneCtas = 4;   // CTAs (one cluster) per utterance
 constexpr int kPruneMaxK = 128;
 #define B200_PRUNE_LZ (-10000000000.0f)
 
@@ -53,20 +57,71 @@ __device__ __forceinline__ uint32_t prune_key(float f) {
   return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
 }
 
-__global__ void __launch_bounds__(kPruneThreads) beam_prune_kernel(PruneParams p) {
-  __shared__ int s_hist[256];
+// A cluster of kPruneCtas CTAs per utterance: CTA r owns the r-th contiguous quarter of the utterance's beam * V elements
+// (32 utterances alone would use 32 of 148 SMs, and every pass is latency per warp, not traffic), the digit histograms
+// are merged through distributed shared memory, every CTA takes the same decision from the merged histogram, and the
+// winners are collected in CTA 0's shared memory.
+__global__ void __cluster_dims__(kPruneCtas, 1, 1) __launch_bounds__(kPruneThreads) beam_prune_kernel(PruneParams p) {
+  cg::cluster_group cluster = cg::this_cluster();
+  __shared__ int s_hist[256];     // this CTA's histogram of the current digit
+  __shared__ int s_tot[256];      // the cluster's
   __shared__ uint32_t s_prefix;   // the bits of the k-th largest key decided so far
   __shared__ int s_need;          // how many of the elements that match the prefix are still wanted
   __shared__ int s_scan[kPruneThreads / 32];
-  __shared__ int s_cnt;
+  __shared__ int s_ties;          // ties at the threshold inside this CTA's range
+  __shared__ int s_cnt;           // (CTA 0's is the cluster's) elements above the threshold collected so far
   __shared__ float s_val[kPruneMaxK];
   __shared__ int s_idx[kPruneMaxK];
-  const int u = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int r = (int)cluster.block_rank();
+  const int u = blockIdx.x / kPruneCtas, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n = p.beam * p.V;
   if (tid == 0) { s_prefix = 0; s_need = p.k; s_cnt = 0; }
   // eos scores of the utterance's hypotheses (:841)
-  for (int h = tid; h < p.beam; h += kPruneThreads)
-    p.eos_v[u * p.beam + h] = __fadd_rn(prune_local(p, u * p.beam + h, h, p.eos), p.vs[u * p.beam + h]);
+  if (r == 0)
+    for (int h = tid; h < p.beam; h += kPruneThreads)
+      p.eos_v[u * p.beam + h] = __fadd_rn(prune_local(p, u * p.beam + h, h, p.eos), p.vs[u * p.beam + h]);
+
+  // Every warp owns a contiguous range of the CTA's elements and walks it 32 elements at a time, four such rows per
+  // trip with their eight loads issued before the first is used (the two score matrices sit in L2).
+  constexpr int kWarps = kPruneThreads / 32;
+  const int per_cta = (((n + kPruneCtas - 1) / kPruneCtas) + 31) & ~31;
+  const int c0 = min(r * per_cta, n), c1 = min(c0 + per_cta, n);
+  const int per_warp = (((c1 - c0 + kWarps - 1) / kWarps) + 31) & ~31;
+  const int w0 = min(c0 + warp * per_warp, c1), w1 = min(w0 + per_warp, c1);
+  auto walk = [&](auto&& visit) {  // visit(valid, j, value): called by all 32 lanes together, j ascending
+    for (int base = w0; base < w1; base += 128) {
+      float a[4], c4[4], vs[4];
+      int jj[4];
+      bool ok[4], eosc[4], zero[4], dead[4];
+#pragma unroll
+      for (int x = 0; x < 4; ++x) {
+        const int j = base + 32 * x + lane;
+        jj[x] = j;
+        ok[x] = j < w1;
+        const int jc = ok[x] ? j : w0;
+        const int h = jc / p.V, c = jc - h * p.V;
+        const int64_t o = (int64_t)(u * p.beam + h) * p.V + c;
+        a[x] = p.att[o];
+        c4[x] = p.ctc ? p.ctc[o] : 0.f;
+        vs[x] = p.vs[u * p.beam + h];
+        eosc[x] = c == p.eos;
+        zero[x] = c == 0;
+        dead[x] = p.first && h >= 1;
+      }
+#pragma unroll
+      for (int x = 0; x < 4; ++x) {
+        // the reference's operations in the reference's order (prune_local / prune_value)
+        float v = __fmul_rn(p.att_w, a[x]);
+        if (p.ctc) {
+          if (zero[x]) v = B200_PRUNE_LZ;
+          v = __fadd_rn(v, __fmul_rn(p.ctc_w, c4[x]));
+        }
+        if (dead[x]) v = B200_PRUNE_LZ;
+        v = eosc[x] ? B200_PRUNE_LZ : __fadd_rn(vs[x], v);
+        visit(ok[x], jj[x], v);
+      }
+    }
+  };
 
   // ---- radix select: after pass d the top 8*(d+1) bits of the k-th largest key are known
   for (int d = 0; d < 4; ++d) {
@@ -75,12 +130,20 @@ __global__ void __launch_bounds__(kPruneThreads) beam_prune_kernel(PruneParams p
     __syncthreads();
     const uint32_t prefix = s_prefix;
     const uint32_t mask = d == 0 ? 0u : (0xffffffffu << (shift + 8));
-    for (int h = 0; h < p.beam; ++h) {
-      const float vsh = p.vs[u * p.beam + h];
-      for (int c = tid; c < p.V; c += kPruneThreads) {
-        const uint32_t key = prune_key(prune_value(p, u, h, c, vsh));
-        if ((key & mask) == prefix) atomicAdd(&s_hist[(key >> shift) & 255u], 1);
-      }
+    walk([&](bool ok, int, float v) {
+      const uint32_t key = prune_key(v);
+      const bool act = ok && (key & mask) == prefix;
+      // scores of one utterance crowd into a few buckets: one shared-memory atomic per distinct bucket of the warp
+      const uint32_t bucket = act ? ((key >> shift) & 255u) : 256u;
+      const unsigned peers = __match_any_sync(0xffffffffu, bucket);
+      if (act && lane == __ffs(peers) - 1) atomicAdd(&s_hist[bucket], __popc(peers));
+    });
+    cluster.sync();  // the histograms of all CTAs are complete
+    if (tid < 256) {
+      int t = 0;
+#pragma unroll
+      for (int rr = 0; rr < kPruneCtas; ++rr) t += *cluster.map_shared_rank(&s_hist[tid], rr);
+      s_tot[tid] = t;
     }
     __syncthreads();
     if (warp == 0) {
@@ -89,7 +152,7 @@ __global__ void __launch_bounds__(kPruneThreads) beam_prune_kernel(PruneParams p
       int c8[8];
       int tot = 0;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { c8[j] = s_hist[255 - (lane * 8 + j)]; tot += c8[j]; }   // lane 0 holds the largest buckets
+      for (int j = 0; j < 8; ++j) { c8[j] = s_tot[255 - (lane * 8 + j)]; tot += c8[j]; }   // lane 0 holds the largest buckets
       int incl = tot;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -111,39 +174,27 @@ __global__ void __launch_bounds__(kPruneThreads) beam_prune_kernel(PruneParams p
         if (lane == 0) { s_prefix = prefix | ((uint32_t)found << shift); s_need = left; }
       }
     }
-    __syncthreads();
+    cluster.sync();  // every CTA has read this histogram (it is zeroed next); s_prefix / s_need are set
   }
   const uint32_t thr = s_prefix;   // key of the k-th largest value
   const int ties_wanted = s_need;  // how many elements EQUAL to it belong to the top k (>= 1)
 
-  // ---- collect: everything above the threshold, and the first `ties_wanted` ties in index order.  Every thread owns a
-  //      contiguous range of indices so that "in index order" is a block-wide exclusive scan of the tie counts.
-  const int per = (n + kPruneThreads - 1) / kPruneThreads;
-  const int j0 = min(tid * per, n), j1 = min(j0 + per, n);
-  int my_ties = 0;
-  {
-    int h = j0 / p.V, c = j0 - h * p.V;
-    float vsh = h < p.beam ? p.vs[u * p.beam + h] : 0.f;
-    for (int j = j0; j < j1; ++j) {
-      const float v = prune_value(p, u, h, c, vsh);
-      const uint32_t key = prune_key(v);
-      if (key > thr) {
-        const int slot = atomicAdd(&s_cnt, 1);
-        if (slot < kPruneMaxK) { s_val[slot] = v; s_idx[slot] = j; }
-      } else if (key == thr) {
-        ++my_ties;
-      }
-      if (++c == p.V) { c = 0; ++h; if (h < p.beam) vsh = p.vs[u * p.beam + h]; }
+  // ---- collect into CTA 0: everything above the threshold, and the first `ties_wanted` ties in index order -- the
+  //      ranges of the CTAs and of their warps are contiguous and ascending, so "in index order" is the ties of the
+  //      CTAs before this one, plus those of the warps before this one, plus the position inside the warp's own walk.
+  float* val0 = cluster.map_shared_rank(s_val, 0);
+  int* idx0 = cluster.map_shared_rank(s_idx, 0);
+  int* cnt0 = cluster.map_shared_rank(&s_cnt, 0);
+  int my_ties = 0;  // (warp-uniform)
+  walk([&](bool ok, int j, float v) {
+    const uint32_t key = prune_key(v);
+    if (ok && key > thr) {
+      const int slot = atomicAdd(cnt0, 1);
+      if (slot < kPruneMaxK) { val0[slot] = v; idx0[slot] = j; }
     }
-  }
-  // exclusive scan of my_ties over the block
-  int incl = my_ties;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int t = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += t;
-  }
-  if (lane == 31) s_scan[warp] = incl;
+    my_ties += __popc(__ballot_sync(0xffffffffu, ok && key == thr));
+  });
+  if (lane == 0) s_scan[warp] = my_ties;
   __syncthreads();
   if (warp == 0) {
     int w = s_scan[lane];
@@ -153,40 +204,42 @@ __global__ void __launch_bounds__(kPruneThreads) beam_prune_kernel(PruneParams p
       if (lane >= o) w += t;
     }
     s_scan[lane] = w;   // inclusive over warps
+    if (lane == 31) s_ties = w;
   }
-  __syncthreads();
-  int rank = incl - my_ties + (warp ? s_scan[warp - 1] : 0);   // ties before this thread's range
-  const int above = s_cnt;                                     // (all `key > thr` elements are in by the barriers above)
+  cluster.sync();  // all elements above the threshold are in CTA 0; the CTAs' tie counts are visible
+  int rank = warp ? s_scan[warp - 1] : 0;   // ties in the ranges before this warp's
+  for (int rr = 0; rr < r; ++rr) rank += *cluster.map_shared_rank(&s_ties, rr);
+  const int above = *cnt0;
   if (my_ties && rank < ties_wanted) {
-    int h = j0 / p.V, c = j0 - h * p.V;
-    float vsh = p.vs[u * p.beam + h];
-    for (int j = j0; j < j1 && rank < ties_wanted; ++j) {
-      const float v = prune_value(p, u, h, c, vsh);
-      if (prune_key(v) == thr) {
-        const int slot = above + rank;
-        if (slot < kPruneMaxK) { s_val[slot] = v; s_idx[slot] = j; }
-        ++rank;
+    walk([&](bool ok, int j, float v) {
+      const bool is_tie = ok && prune_key(v) == thr;
+      const unsigned tie = __ballot_sync(0xffffffffu, is_tie);
+      const int mine = rank + __popc(tie & ((1u << lane) - 1u));
+      if (is_tie && mine < ties_wanted) {
+        const int slot = above + mine;
+        if (slot < kPruneMaxK) { val0[slot] = v; idx0[slot] = j; }
       }
-      if (++c == p.V) { c = 0; ++h; if (h < p.beam) vsh = p.vs[u * p.beam + h]; }
-    }
+      rank += __popc(tie);
+    });
   }
-  __syncthreads();
+  cluster.sync();  // CTA 0 holds the k winners; the other CTAs are done (nobody reads their shared memory any more)
+  if (r != 0) return;
   // ---- the k winners, sorted: value descending, index ascending (rank by counting)
   const int k = min(p.k, kPruneMaxK);
   if (tid < k) {
     const float v = s_val[tid];
     const int j = s_idx[tid];
     const uint32_t key = prune_key(v);
-    int r = 0;
+    int rk = 0;
     for (int o = 0; o < k; ++o) {
       const uint32_t ko = prune_key(s_val[o]);
-      r += (ko > key || (ko == key && s_idx[o] < j)) ? 1 : 0;
+      rk += (ko > key || (ko == key && s_idx[o] < j)) ? 1 : 0;
     }
-    p.best_scores[(int64_t)u * p.k + r] = v;
-    p.best_ids[(int64_t)u * p.k + r] = j;
+    p.best_scores[(int64_t)u * p.k + rk] = v;
+    p.best_ids[(int64_t)u * p.k + rk] = j;
     const int h = j / p.V;
-    p.tok[(int64_t)u * p.k + r] = j - h * p.V;
-    p.vidx[(int64_t)u * p.k + r] = h + u * p.beam;
+    p.tok[(int64_t)u * p.k + rk] = j - h * p.V;
+    p.vidx[(int64_t)u * p.k + rk] = h + u * p.beam;
   }
 }
 
@@ -211,7 +264,7 @@ extern "C" int b200_beam_prune(const float* att_logp, const float* ctc_scores, c
   p.batch = (int)batch; p.beam = (int)beam; p.V = (int)V; p.k = (int)k; p.eos = eos; p.first = first_position ? 1 : 0;
   p.att_w = att_weight; p.ctc_w = ctc_weight;
   p.best_scores = best_scores; p.best_ids = best_ids; p.eos_v = eos_vscores; p.tok = tokens; p.vidx = parent_rows;
-  beam_prune_kernel<<<(unsigned)batch, kPruneThreads, 0, (cudaStream_t)stream>>>(p);
+  beam_prune_kernel<<<(unsigned)batch * kPruneCtas, kPruneThreads, 0, (cudaStream_t)stream>>>(p);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }

@@ -112,16 +112,22 @@ class CTCPrefixScoreB200(object):
             _lib.check(rc, "b200_ctc_prefix_columns")
         return self._xc
 
-    def __call__(self, y, state, scoring_ids=None, att_w=None):
+    def __call__(self, y, state, scoring_ids=None, att_w=None, last_ids=None):
         """Compute CTC prefix scores for next labels.
 
         :param list y: prefix label sequences (n_bh lists, or a (n_bh, len) tensor)
         :param tuple state: previous CTC state (from index_select_state) or None
         :param torch.Tensor scoring_ids: candidates per hypothesis (n_bh, snum) or None for all O
         :param torch.Tensor att_w: attention weights (n_bh, T) to decide the CTC window
+        :param torch.Tensor last_ids: (not in the reference) the last label of every prefix as a contiguous int64
+            CUDA tensor (n_bh,), for a search loop that has it already: saves the strided copy out of y
         :return: (ctc_local_scores (n_bh, O), new_state)
         """
-        if torch.is_tensor(y):
+        if last_ids is not None and torch.is_tensor(y):
+            output_length = y.size(1) - 1
+            if last_ids.device != self.device or last_ids.dtype != torch.int64 or not last_ids.is_contiguous():
+                last_ids = last_ids.to(device=self.device, dtype=torch.int64).contiguous()
+        elif torch.is_tensor(y):
             output_length = y.size(1) - 1
             last_ids = y[:, -1]
             if last_ids.device != self.device or last_ids.dtype != torch.int64:

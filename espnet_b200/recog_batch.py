@@ -13,14 +13,16 @@ comprehensions per step), the scorer is given that tensor directly, and the host
 (the rows the end conditions need: eos scores, the beam threshold, the survivors' ids), because "which hypotheses have
 ended" and "may the search stop" are host decisions in the reference as well.
 """
+import math
+
 import numpy as np
 import torch
 
 from . import _lib
-from .batch_beam_search import end_detect
 from .ctc_prefix_score import CTCPrefixScoreB200
 
 LOGZERO = -10000000000.0          # decoders.py:84
+END_DETECT_D = math.log(1 * math.exp(-10))   # e2e_asr_common.py:21
 CTC_SCORING_RATIO = 1.5           # decoders.py:25
 
 
@@ -43,13 +45,14 @@ class DecoderStep(object):
         raise NotImplementedError
 
 
-def beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, first_position):
+def beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, first_position, packed=False):
     """decoders.py:812-852 in ONE kernel (``b200_beam_prune``, csrc/beam_prune.cu): the joint local scores, the eos
     scores, the accumulated scores and the per-utterance top-k over beam x V.
 
     logp (batch*beam, V) fp32 log-softmax of the attention decoder; ctc_scores the same shape or None;
     vscores (batch, beam).  Returns (best_scores (batch, beam), best_ids (batch, beam) in hyp * V + token space,
-    eos_vscores (batch, beam), tokens (batch*beam,), parent_rows (batch*beam,))."""
+    eos_vscores (batch, beam), tokens (batch*beam,), parent_rows (batch*beam,)); packed=True: the two buffers they
+    are views of, (2, batch, beam) float32 [best_scores, eos_vscores] and (3, batch, beam) int64 [ids, tokens, rows]."""
     batch, beam = vscores.shape
     V = logp.size(-1)
     dev = logp.device
@@ -57,14 +60,14 @@ def beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, first_pos
     if ctc_scores is not None:
         ctc_scores = ctc_scores.contiguous()
     vscores = vscores.contiguous()
-    best_scores = torch.empty((batch, beam), dtype=torch.float32, device=dev)
-    eos_v = torch.empty((batch, beam), dtype=torch.float32, device=dev)
+    sc = torch.empty((2, batch, beam), dtype=torch.float32, device=dev)  # best_scores, eos_vscores
     ids = torch.empty((3, batch, beam), dtype=torch.int64, device=dev)   # best_ids, tokens, parent rows
     nb = batch * beam * 8
+    sp = sc.data_ptr()
     idx = dev.index if dev.index is not None else torch.cuda.current_device()
     args = (logp.data_ptr(), None if ctc_scores is None else ctc_scores.data_ptr(), vscores.data_ptr(), batch, beam, V, beam,
-            float(att_weight), float(ctc_weight), int(eos), 1 if first_position else 0, best_scores.data_ptr(),
-            ids.data_ptr(), eos_v.data_ptr(), ids.data_ptr() + nb, ids.data_ptr() + 2 * nb,
+            float(att_weight), float(ctc_weight), int(eos), 1 if first_position else 0, sp,
+            ids.data_ptr(), sp + 4 * batch * beam, ids.data_ptr() + nb, ids.data_ptr() + 2 * nb,
             torch._C._cuda_getCurrentRawStream(idx))
     fn = _lib.load().b200_beam_prune
     if torch.cuda.current_device() == idx:   # (the device guard only where the current device is another)
@@ -73,7 +76,28 @@ def beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, first_pos
         with torch.cuda.device(dev):
             rc = fn(*args)
     _lib.check(rc, "b200_beam_prune")
-    return best_scores, ids[0], eos_v, ids[1].view(-1), ids[2].view(-1)
+    if packed:
+        return sc, ids
+    return sc[0], ids[0], sc[1], ids[1].view(-1), ids[2].view(-1)
+
+
+def _add_ended(ended, summary, yseq, v):
+    """An ended hypothesis, and what end detection needs of it: the best score overall and per length."""
+    score = np.float32(v)
+    ended.append({"yseq": yseq, "vscore": v, "score": score})
+    sc, n = float(score), len(yseq)
+    if summary[0] is None or sc > summary[0]:
+        summary[0] = sc
+    if n not in summary[1] or sc > summary[1][n]:
+        summary[1][n] = sc
+
+
+def _end_detect(summary, i, M=3, D_end=END_DETECT_D):
+    """``end_detect`` (e2e_asr_common.py:21-51) from the running summary instead of a pass over all ended hypotheses."""
+    best, by_len = summary
+    if best is None:
+        return False
+    return all((i - m) in by_len and by_len[i - m] - best < D_end for m in range(M))
 
 
 def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, maxlenratio=0.0, minlenratio=0.0,
@@ -98,10 +122,13 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
     minlen = int(minlenratio * max_hlen)
     dev = lpz.device if lpz is not None else torch.device("cuda")
     odim = None
+    own_scorer = False
     if lpz is not None:
         odim = lpz.size(-1)
         if scorer is None:
             scorer = CTCPrefixScoreB200(lpz, torch.as_tensor(hl), 0, eos, margin=ctc_margin)
+            own_scorer = True
+    own_scorer = own_scorer or isinstance(scorer, CTCPrefixScoreB200)
     scoring_num = 0
     if lpz is not None and pre_beam:
         scoring_num = min(int(pre_beam), odim)
@@ -110,26 +137,41 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
     yseq[:, 0] = sos
     vscores = torch.zeros(batch, beam, device=dev)
     ended = [[] for _ in range(batch)]
+    summary = [[None, {}] for _ in range(batch)]   # per utterance: best ended score, best ended score per length
+    live_len = np.asarray(hl).reshape(-1, 1)
+    min_hl = min(hl)
     stop = [False] * batch
     state = decoder.start(n_bb)
     ctc_state = None
+    # Without a pre-beam and without an attention window the CTC scores of a position depend on the prefixes alone:
+    # they are issued BEFORE the decoder step, so that the score kernel runs while the host issues the decoder's kernels
+    early = own_scorer and scoring_num == 0 and not scorer.margin
+    tok = None
     for i in range(maxlen):
         vy = yseq[:, i]
+        ctc_scores = None
+        if early:
+            ctc_scores, ctc_state = scorer(yseq[:, :i + 1], ctc_state, None, None, last_ids=tok)
         logp, att_w, state = decoder.step(vy, state)
         if odim is None:
             odim = logp.size(-1)
-        ctc_scores = None
-        if scorer is not None:
+        if scorer is not None and not early:
             part_ids = None
             if scoring_num > 0:   # pre-beam on the attention scores with the blank masked (:816-822)
                 local = att_weight * logp
                 local[:, 0] = LOGZERO
                 part_ids = torch.topk(local, scoring_num, dim=-1)[1]
-            ctc_scores, ctc_state = scorer(yseq[:, :i + 1], ctc_state, part_ids, att_w)
+            if own_scorer:   # (the last labels are at hand: the previous position's tokens)
+                ctc_scores, ctc_state = scorer(yseq[:, :i + 1], ctc_state, part_ids, att_w, last_ids=tok)
+            else:
+                ctc_scores, ctc_state = scorer(yseq[:, :i + 1], ctc_state, part_ids, att_w)
         if fused and logp.dtype == torch.float32 and beam <= 128 and beam * odim < 2 ** 31:
             # joint local scores, eos scores, accumulated scores and the per-utterance top-k in one kernel
-            best_scores, best_ids, eos_v, tok, vidx = beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, i == 0)
+            sc_pack, id_pack = beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, i == 0, packed=True)
+            best_scores, eos_v = sc_pack[0], sc_pack[1]
+            best_ids, tok, vidx = id_pack[0], id_pack[1].view(-1), id_pack[2].view(-1)
         else:
+            sc_pack = None
             local = att_weight * logp
             if scorer is not None:
                 local[:, 0] = LOGZERO  # avoid choosing blank (:816)
@@ -149,33 +191,41 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
         yseq[:, i + 1] = tok
         vscores = best_scores
         state = decoder.select(state, vidx)
-        # pick ended hypotheses (:896-928): ONE device->host copy with everything the host decides on
+        # pick ended hypotheses (:896-928): ONE device->host copy with everything the host decides on; the comparison
+        # runs over the whole (batch, beam) array at once and Python only visits the hypotheses that did end
         if i >= minlen:
-            packed = torch.cat([eos_v, best_scores], dim=1).cpu().numpy()
-            eos_h, best_h = packed[:, :beam], packed[:, beam:]
+            if sc_pack is not None:
+                packed = sc_pack.cpu().numpy()
+                best_h, eos_h = packed[0], packed[1]
+            else:
+                packed = torch.cat([eos_v, best_scores], dim=1).cpu().numpy()
+                eos_h, best_h = packed[:, :beam], packed[:, beam:]
             pen = (i + 1) * penalty
-            need_prev = need_cur = None
-            for s in range(batch):
-                if stop[s]:
-                    continue
-                thr = best_h[s, -1]
-                for j in range(beam):
+            hit = eos_h > best_h[:, -1:]
+            if i + 1 > min_hl:
+                hit &= live_len >= i + 1          # len(yk) <= hlens (:908-911); y_prev rows hold i + 1 tokens
+            visit = hit if i < maxlen - 1 else np.ones_like(hit)
+            if any(stop):
+                visit = visit & ~np.asarray(stop)[:, None]
+            if visit.any():
+                need_prev = need_cur = None
+                for s, j in zip(*np.nonzero(visit)):
                     k = s * beam + j
-                    if eos_h[s, j] > thr:
-                        if i + 1 <= hl[s]:   # len(yk) <= hlens (:908-911); y_prev rows hold i + 1 tokens
+                    if eos_h[s, j] > best_h[s, -1]:
+                        if hit[s, j]:
                             if need_prev is None:
                                 need_prev = y_prev[:, :i + 1].cpu().numpy()
                             v = float(eos_h[s, j]) + pen
-                            if v:                      # (`if _vscore:` in the reference: a score of exactly 0 is dropped)
-                                ended[s].append({"yseq": need_prev[k].tolist() + [eos], "vscore": v, "score": np.float32(v)})
-                    elif i == maxlen - 1:
+                            if v:                  # (`if _vscore:` in the reference: a score of exactly 0 is dropped)
+                                _add_ended(ended[s], summary[s], need_prev[k].tolist() + [eos], v)
+                    else:                          # i == maxlen - 1: the survivors end here
                         if need_cur is None:
                             need_cur = yseq[:, :i + 2].cpu().numpy()
                         v = float(best_h[s, j]) + pen
                         if v:
-                            ended[s].append({"yseq": need_cur[k].tolist() + [eos], "vscore": v, "score": np.float32(v)})
+                            _add_ended(ended[s], summary[s], need_cur[k].tolist() + [eos], v)
         # end detection (:931-937)
-        stop = [stop[s] or end_detect([(len(h["yseq"]), float(h["score"])) for h in ended[s]], i) for s in range(batch)]
+        stop = [stop[s] or _end_detect(summary[s], i) for s in range(batch)]
         if all(stop):
             break
         if scorer is not None:

@@ -106,3 +106,25 @@ def test_pack_labels_host_and_mixed_inputs():
     out = pack_labels([3, 4, 5], torch.tensor([0, 2]), torch.tensor([7, 9], dtype=torch.int32), [2, 1], torch.device("cpu"))
     assert [o.tolist() for o in out] == [[3, 4, 5], [0, 2], [7, 9], [2, 1]]
     assert all(o.dtype == torch.int64 for o in out)
+
+
+def test_running_end_detection_equals_the_list_form():
+    """recog_batch keeps (best score, best score per length) instead of re-reading every ended hypothesis at every
+    position: the same decisions as end_detect (e2e_asr_common.py:21-51) on a random stream of ended hypotheses."""
+    import random
+
+    from espnet_b200.batch_beam_search import end_detect
+    from espnet_b200.recog_batch import _add_ended, _end_detect
+
+    rng = random.Random(5)
+    seen = {True: 0, False: 0}
+    for trial in range(200):
+        ended, summary = [], [None, {}]
+        for i in range(12):
+            for _ in range(rng.randrange(0, 3)):
+                v = -rng.random() * (2.0 if rng.random() < 0.5 else 40.0) - 0.1 * i
+                _add_ended(ended, summary, [0] * (i + 2), v)      # hypotheses that end at position i hold i + 2 tokens
+            want = end_detect([(len(h["yseq"]), float(h["score"])) for h in ended], i)
+            assert _end_detect(summary, i) == want
+            seen[want] += 1
+    assert seen[True] > 0 and seen[False] > 0
