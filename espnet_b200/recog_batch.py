@@ -186,6 +186,8 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
             best_scores, best_ids = torch.topk(acc.view(batch, -1), beam, 1)
             tok = torch.fmod(best_ids, odim).view(-1)
             vidx = (torch.div(best_ids, odim, rounding_mode="floor") + pad_b).view(-1)
+        if scorer is not None:   # (before the host waits for this position's scores: the kernel runs under the wait)
+            ctc_state = scorer.index_select_state(ctc_state, best_ids)
         y_prev = yseq
         yseq = yseq.index_select(0, vidx)
         yseq[:, i + 1] = tok
@@ -228,8 +230,6 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
         stop = [stop[s] or _end_detect(summary[s], i) for s in range(batch)]
         if all(stop):
             break
-        if scorer is not None:
-            ctc_state = scorer.index_select_state(ctc_state, best_ids)
     if stats is not None:
         stats["steps"] = i + 1
     out = []
