@@ -27,6 +27,10 @@
  *   b200_ctc_prefix_score
  *       espnet/nets/ctc_prefix_score.py:69-188 (CTCPrefixScoreTH.__call__), the
  *       score half: log_psi - s_prev for every (hypothesis, candidate).
+ *   b200_ctc_prefix_columns / b200_ctc_prefix_score_columns
+ *       the same call with scoring_ids (ctc_prefix_score.py:100-115, :159-163: the
+ *       candidates' columns gathered with index_select; the pre-beam of
+ *       espnet/nets/batch_beam_search.py:228-238) from a column copy of x.
  *   b200_ctc_prefix_select
  *       espnet/nets/ctc_prefix_score.py:190-221 (index_select_state) and
  *       espnet/nets/scorers/ctc.py:41-64 (select_state): the forward variables
@@ -35,6 +39,12 @@
  *       espnet2/asr/ctc.py:103-111 (CTC.argmax over the vocabulary).
  *   b200_ctc_viterbi
  *       espnet/nets/pytorch_backend/ctc.py:153-216 (CTC.forced_align).
+ *   b200_beam_prune
+ *       espnet/nets/pytorch_backend/rnn/decoders.py:812-852 (score accumulation and
+ *       per-utterance top-k of Decoder.recognize_beam_batch).
+ *   b200_peer_sum_exchange
+ *       espnet2/torch_utils/recursive_op.py:24,50 (the per-step all-reduces of
+ *       espnet2/train/trainer.py:386-397).
  */
 #ifndef ESPNET_B200_CTC_H_
 #define ESPNET_B200_CTC_H_
