@@ -40,6 +40,7 @@ SIGNATURES = {
                                       _i64, _i64, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "b200_ctc_debug_force_log_sweep": (_int, [_int]),
     "b200_beam_prune": (_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _f32, _f32, _int, _int, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b200_pre_beam_candidates": (_int, [_vp, _i64, _i64, _i64, _f32, _int, _vp, _vp]),
     "b200_ctc_debug_prefix_fp32_score": (None, [_int]),
     "b200_ctc_debug_single_cta_sweep": (None, [_int]),
     "b200_ctc_stage_labels": (_int, [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _vp, _vp]),

@@ -243,6 +243,118 @@ __global__ void __cluster_dims__(kPruneCtas, 1, 1) __launch_bounds__(kPruneThrea
   }
 }
 
+// ------------------------------------------------------------------------------------------------ pre-beam candidates
+// decoders.py:816-822 / batch_beam_search.py:228-238: the k best tokens of every hypothesis by the attention score,
+//     local = att_weight * logp; local[:, blank] = logzero; topk(local, k)[1]
+// (three eager launches, ~100 us of host time per position).  One CTA per hypothesis: the row's order-preserving keys
+// go to shared memory once, the 4 x 8-bit radix select and the collection run there; ties in index order, ids sorted
+// by value (descending) then index.
+constexpr int kCandThreads = 256;
+__global__ void __launch_bounds__(kCandThreads) pre_beam_topk_kernel(const float* __restrict__ logp, int V, int k, float w, int blank,
+                                                                     int64_t* __restrict__ ids) {
+  extern __shared__ uint32_t s_key[];  // [V]
+  __shared__ int s_hist[256];
+  __shared__ uint32_t s_prefix;
+  __shared__ int s_need, s_cnt;
+  __shared__ int s_scan[kCandThreads / 32];
+  __shared__ uint32_t s_wkey[kPruneMaxK];
+  __shared__ int s_widx[kPruneMaxK];
+  const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int kWarps = kCandThreads / 32;
+  const float* x = logp + (int64_t)row * V;
+  for (int c = tid; c < V; c += kCandThreads) {
+    float v = __fmul_rn(w, x[c]);
+    if (c == blank) v = B200_PRUNE_LZ;
+    s_key[c] = prune_key(v);
+  }
+  if (tid == 0) { s_prefix = 0; s_need = k; s_cnt = 0; }
+  // contiguous, ascending ranges per warp (so that "in index order" is a scan over the warps)
+  const int per_warp = (((V + kWarps - 1) / kWarps) + 31) & ~31;
+  const int w0 = min(warp * per_warp, V), w1 = min(w0 + per_warp, V);
+  for (int d = 0; d < 4; ++d) {
+    const int shift = 24 - 8 * d;
+    s_hist[tid] = 0;  // (256 threads, 256 buckets)
+    __syncthreads();
+    const uint32_t prefix = s_prefix;
+    const uint32_t mask = d == 0 ? 0u : (0xffffffffu << (shift + 8));
+    for (int base = w0; base < w1; base += 32) {
+      const int c = base + lane;
+      const uint32_t key = c < w1 ? s_key[c] : 0u;
+      const bool act = c < w1 && (key & mask) == prefix;
+      const uint32_t bucket = act ? ((key >> shift) & 255u) : 256u;
+      const unsigned peers = __match_any_sync(0xffffffffu, bucket);
+      if (act && lane == __ffs(peers) - 1) atomicAdd(&s_hist[bucket], __popc(peers));
+    }
+    __syncthreads();
+    if (warp == 0) {
+      const int need = s_need;
+      int c8[8];
+      int tot = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { c8[j] = s_hist[255 - (lane * 8 + j)]; tot += c8[j]; }
+      int incl = tot;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      int before = incl - tot;
+      int found = -1, left = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (found < 0 && before < need && before + c8[j] >= need) { found = 255 - (lane * 8 + j); left = need - before; }
+        before += c8[j];
+      }
+      const unsigned who = __ballot_sync(0xffffffffu, found >= 0);
+      if (who) {
+        const int src = __ffs(who) - 1;
+        found = __shfl_sync(0xffffffffu, found, src);
+        left = __shfl_sync(0xffffffffu, left, src);
+        if (lane == 0) { s_prefix = prefix | ((uint32_t)found << shift); s_need = left; }
+      }
+    }
+    __syncthreads();
+  }
+  const uint32_t thr = s_prefix;
+  const int ties_wanted = s_need;
+  int my_ties = 0;
+  for (int base = w0; base < w1; base += 32) {
+    const int c = base + lane;
+    const uint32_t key = c < w1 ? s_key[c] : 0u;
+    if (c < w1 && key > thr) {
+      const int slot = atomicAdd(&s_cnt, 1);
+      if (slot < kPruneMaxK) { s_wkey[slot] = key; s_widx[slot] = c; }
+    }
+    my_ties += __popc(__ballot_sync(0xffffffffu, c < w1 && key == thr));
+  }
+  if (lane == 0) s_scan[warp] = my_ties;
+  __syncthreads();
+  int rank = 0;
+  for (int q = 0; q < warp; ++q) rank += s_scan[q];
+  const int above = s_cnt;
+  if (my_ties && rank < ties_wanted) {
+    for (int base = w0; base < w1; base += 32) {
+      const int c = base + lane;
+      const bool is_tie = c < w1 && s_key[c] == thr;
+      const unsigned tie = __ballot_sync(0xffffffffu, is_tie);
+      const int mine = rank + __popc(tie & ((1u << lane) - 1u));
+      if (is_tie && mine < ties_wanted) {
+        const int slot = above + mine;
+        if (slot < kPruneMaxK) { s_wkey[slot] = thr; s_widx[slot] = c; }
+      }
+      rank += __popc(tie);
+    }
+  }
+  __syncthreads();
+  if (tid < k) {
+    const uint32_t key = s_wkey[tid];
+    const int c = s_widx[tid];
+    int r = 0;
+    for (int o = 0; o < k; ++o) r += (s_wkey[o] > key || (s_wkey[o] == key && s_widx[o] < c)) ? 1 : 0;
+    ids[(int64_t)row * k + r] = c;
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -265,6 +377,21 @@ extern "C" int b200_beam_prune(const float* att_logp, const float* ctc_scores, c
   p.att_w = att_weight; p.ctc_w = ctc_weight;
   p.best_scores = best_scores; p.best_ids = best_ids; p.eos_v = eos_vscores; p.tok = tokens; p.vidx = parent_rows;
   beam_prune_kernel<<<(unsigned)batch * kPruneCtas, kPruneThreads, 0, (cudaStream_t)stream>>>(p);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+extern "C" int b200_pre_beam_candidates(const float* att_logp, int64_t n_rows, int64_t V, int64_t k, float att_weight, int blank,
+                                        int64_t* ids, void* stream) {
+  B200_CHECK_ARG(att_logp && ids, B200_ERR_INVALID_ARGUMENT, "null pointer argument");
+  B200_CHECK_ARG(n_rows >= 1 && V >= 1 && n_rows < (1ll << 31), B200_ERR_INVALID_ARGUMENT, "need n_rows>=1, V>=1, got n_rows=%lld V=%lld",
+                 (long long)n_rows, (long long)V);
+  B200_CHECK_ARG(k >= 1 && k <= kPruneMaxK && k <= V, B200_ERR_UNSUPPORTED_SHAPE, "k=%lld must lie in [1, min(%d, V)]", (long long)k,
+                 kPruneMaxK);
+  const size_t smem = sizeof(uint32_t) * (size_t)V;
+  B200_CHECK_ARG(smem <= 200u * 1024u, B200_ERR_UNSUPPORTED_SHAPE, "V=%lld: a row of keys does not fit shared memory", (long long)V);
+  if (smem > 40u * 1024u) B200_CUDA(set_max_smem_cached((const void*)pre_beam_topk_kernel, (int)smem));
+  pre_beam_topk_kernel<<<(unsigned)n_rows, kCandThreads, smem, (cudaStream_t)stream>>>(att_logp, (int)V, (int)k, att_weight, blank, ids);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }

@@ -81,6 +81,25 @@ def beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, first_pos
     return sc[0], ids[0], sc[1], ids[1].view(-1), ids[2].view(-1)
 
 
+def pre_beam_candidates(logp, k, att_weight, blank=0):
+    """decoders.py:816-822 in ONE kernel (``b200_pre_beam_candidates``): the k best tokens of every hypothesis by
+    ``att_weight * logp`` with the blank masked; logp (n, V) fp32 -> ids (n, k) int64, best first."""
+    n, V = logp.shape
+    logp = logp.contiguous()
+    ids = torch.empty((n, k), dtype=torch.int64, device=logp.device)
+    dev = logp.device
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    args = (logp.data_ptr(), n, V, int(k), float(att_weight), int(blank), ids.data_ptr(), torch._C._cuda_getCurrentRawStream(idx))
+    fn = _lib.load().b200_pre_beam_candidates
+    if torch.cuda.current_device() == idx:
+        rc = fn(*args)
+    else:
+        with torch.cuda.device(dev):
+            rc = fn(*args)
+    _lib.check(rc, "b200_pre_beam_candidates")
+    return ids
+
+
 def _add_ended(ended, summary, yseq, v):
     """An ended hypothesis, and what end detection needs of it: the best score overall and per length."""
     score = np.float32(v)
@@ -158,9 +177,12 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
         if scorer is not None and not early:
             part_ids = None
             if scoring_num > 0:   # pre-beam on the attention scores with the blank masked (:816-822)
-                local = att_weight * logp
-                local[:, 0] = LOGZERO
-                part_ids = torch.topk(local, scoring_num, dim=-1)[1]
+                if fused and logp.dtype == torch.float32 and scoring_num <= 128 and odim <= 51200:
+                    part_ids = pre_beam_candidates(logp, scoring_num, att_weight, 0)
+                else:
+                    local = att_weight * logp
+                    local[:, 0] = LOGZERO
+                    part_ids = torch.topk(local, scoring_num, dim=-1)[1]
             if own_scorer:   # (the last labels are at hand: the previous position's tokens)
                 ctc_scores, ctc_state = scorer(yseq[:, :i + 1], ctc_state, part_ids, att_w, last_ids=tok)
             else:

@@ -207,6 +207,13 @@ int b200_beam_prune(const float* att_logp, const float* ctc_scores, const float*
                     int first_position, float* best_scores, int64_t* best_ids, float* eos_vscores,
                     int64_t* tokens, int64_t* parent_rows, void* stream);
 
+/* The pre-beam of the search loops (rnn/decoders.py:816-822, batch_beam_search.py:228-238):
+ *   local = att_weight * att_logp; local[:, blank] = logzero; ids = topk(local, k)[1]
+ * for every row of att_logp (n_rows, V) fp32, in one kernel.  ids int64 (n_rows, k), sorted by
+ * value (descending), equal values in index order.  k <= 128, V <= 51200. */
+int b200_pre_beam_candidates(const float* att_logp, int64_t n_rows, int64_t V, int64_t k,
+                             float att_weight, int blank, int64_t* ids, void* stream);
+
 /* Developer switch: on != 0 runs the lattice sweeps of utterances with 256 <= Lmax + 1 <= 1024 in one CTA per
  * (utterance, direction) instead of a 4-CTA thread-block cluster (A/B timing; the tests run both). */
 void b200_ctc_debug_single_cta_sweep(int on);

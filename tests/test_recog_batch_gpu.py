@@ -143,3 +143,33 @@ def test_beam_prune_ties_are_taken_in_index_order():
     vs = torch.zeros(2, 2, device=dev)
     s, ids, _, _, _ = beam_prune(logp, None, vs, 9, 1.0, 0.0, False)
     assert ids.tolist() == [[0, 1], [0, 1]] and (s == -1.0).all()
+
+
+@pytest.mark.parametrize("n,V,k", [(320, 5000, 15), (7, 33, 5), (3, 50, 50), (1, 2, 1), (60, 12000, 90), (4, 300, 128)])
+def test_pre_beam_candidates_equal_the_eager_lines(n, V, k):
+    """b200_pre_beam_candidates against decoders.py:816-822: the same values in the same order (the ids wherever the
+    values are distinct), blank never chosen unless k forces it."""
+    from espnet_b200.recog_batch import LOGZERO, pre_beam_candidates
+
+    g = torch.Generator(device="cuda").manual_seed(31 * n + V + k)
+    logp = torch.log_softmax(torch.randn(n, V, generator=g, device="cuda") * 4, dim=1)
+    local = 0.7 * logp
+    local[:, 0] = LOGZERO
+    v_ref, id_ref = torch.topk(local, k, dim=-1)
+    ids = pre_beam_candidates(logp, k, 0.7, 0)
+    assert ids.shape == (n, k) and ids.dtype == torch.int64
+    assert torch.equal(local.gather(1, ids), v_ref)
+    assert all(len(set(r)) == k for r in ids.tolist())
+    distinct = (v_ref[:, 1:] != v_ref[:, :-1]).all(1) if k > 1 else torch.ones(n, dtype=torch.bool, device="cuda")
+    if k < V:
+        distinct &= v_ref[:, -1] != torch.topk(local, k + 1, dim=-1)[0][:, -1]
+    assert torch.equal(ids[distinct], id_ref[distinct])
+
+
+def test_pre_beam_candidates_take_ties_in_index_order():
+    from espnet_b200.recog_batch import pre_beam_candidates
+
+    logp = torch.full((2, 40), -2.0, device="cuda")
+    logp[1, 30] = -1.0
+    ids = pre_beam_candidates(logp, 4, 1.0, 0)
+    assert ids.tolist() == [[1, 2, 3, 4], [30, 1, 2, 3]]
