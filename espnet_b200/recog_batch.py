@@ -154,6 +154,7 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
     pad_b = (torch.arange(batch, device=dev) * beam).view(-1, 1)
     yseq = torch.full((n_bb, maxlen + 2), eos, dtype=torch.int64, device=dev)
     yseq[:, 0] = sos
+    yseq_other = torch.empty_like(yseq)
     vscores = torch.zeros(batch, beam, device=dev)
     ended = [[] for _ in range(batch)]
     summary = [[None, {}] for _ in range(batch)]   # per utterance: best ended score, best ended score per length
@@ -167,10 +168,10 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
     early = own_scorer and scoring_num == 0 and not scorer.margin
     tok = None
     for i in range(maxlen):
-        vy = yseq[:, i]
+        vy = yseq.select(1, i)
         ctc_scores = None
         if early:
-            ctc_scores, ctc_state = scorer(yseq[:, :i + 1], ctc_state, None, None, last_ids=tok)
+            ctc_scores, ctc_state = scorer(yseq.narrow(1, 0, i + 1), ctc_state, None, None, last_ids=tok)
         logp, att_w, state = decoder.step(vy, state)
         if odim is None:
             odim = logp.size(-1)
@@ -184,9 +185,9 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
                     local[:, 0] = LOGZERO
                     part_ids = torch.topk(local, scoring_num, dim=-1)[1]
             if own_scorer:   # (the last labels are at hand: the previous position's tokens)
-                ctc_scores, ctc_state = scorer(yseq[:, :i + 1], ctc_state, part_ids, att_w, last_ids=tok)
+                ctc_scores, ctc_state = scorer(yseq.narrow(1, 0, i + 1), ctc_state, part_ids, att_w, last_ids=tok)
             else:
-                ctc_scores, ctc_state = scorer(yseq[:, :i + 1], ctc_state, part_ids, att_w)
+                ctc_scores, ctc_state = scorer(yseq.narrow(1, 0, i + 1), ctc_state, part_ids, att_w)
         if fused and logp.dtype == torch.float32 and beam <= 128 and beam * odim < 2 ** 31:
             # joint local scores, eos scores, accumulated scores and the per-utterance top-k in one kernel
             sc_pack, id_pack = beam_prune(logp, ctc_scores, vscores, eos, att_weight, ctc_weight, i == 0, packed=True)
@@ -211,8 +212,9 @@ def recognize_beam_batch(decoder, lpz, hlens, beam, sos, eos, ctc_weight=0.3, ma
         if scorer is not None:   # (before the host waits for this position's scores: the kernel runs under the wait)
             ctc_state = scorer.index_select_state(ctc_state, best_ids)
         y_prev = yseq
-        yseq = yseq.index_select(0, vidx)
-        yseq[:, i + 1] = tok
+        yseq = torch.index_select(y_prev, 0, vidx, out=yseq_other)   # (two buffers: the survivors' rows, no allocation)
+        yseq_other = y_prev
+        yseq.select(1, i + 1).copy_(tok)
         vscores = best_scores
         state = decoder.select(state, vidx)
         # pick ended hypotheses (:896-928): ONE device->host copy with everything the host decides on; the comparison
