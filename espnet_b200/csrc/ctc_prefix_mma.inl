@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(kMmaConsumers + 32, 7) prefix_score_mma_kernel
             psi[j] = rend;
           } else {
             psi[j] = finish_psi(a, ma + mxs[j], x0s[j]);
-            if ((int64_t)c != last) score_flag(p, a, h, c);
+            if ((int64_t)c != last) score_flag(p, a, h, c, ma);
           }
         }
         float* lp = p.log_psi + (int64_t)h * p.V + c0;

@@ -36,8 +36,11 @@ __device__ __forceinline__ float finish_psi(float acc, float scale_log, float in
   return psi;
 }
 // queue (hypothesis h, token c) for the exact kernel
-__device__ __forceinline__ void score_flag(const ScoreParams& p, float acc, int h, int c) {
-  if (acc < kScoreAccFloor && p.start < p.end) {
+// (m: the maximum of the hypothesis' phi over the window.  At logzero -- a window that does not overlap the frames the
+// prefix has reached -- the exact sum is logzero as well, which is what the scaled sum already returned: nothing to redo.
+// Without this test such a hypothesis queued all V of its tokens: 724 us per position in the windowed search loop.)
+__device__ __forceinline__ void score_flag(const ScoreParams& p, float acc, int h, int c, float m) {
+  if (acc < kScoreAccFloor && p.start < p.end && m > 0.5f * B200_LZ) {
     const int k = atomicAdd(p.w.fix_count, 1);
     p.w.fix_list[k] = h * p.V + c;
   }
@@ -107,7 +110,7 @@ __global__ void __launch_bounds__(kScoreThreads) prefix_score_full_kernel(ScoreP
       } else {
         // (the hypothesis' own last label is overwritten by prefix_score_last_kernel)
         psi = finish_psi(acc[j], p.w.MA[h] + mx, x0);
-        if ((int64_t)c != p.last_ids[h]) score_flag(p, acc[j], h, c);
+        if ((int64_t)c != p.last_ids[h]) score_flag(p, acc[j], h, c, p.w.MA[h]);
       }
       const float sp = p.s_prev ? p.s_prev[h] : 0.f;
       p.log_psi[(int64_t)h * p.V + c] = psi;
@@ -136,7 +139,7 @@ __device__ __forceinline__ void prefix_score_last_warp(const ScoreParams& p, int
   if (lane == 0) {
     const float x0 = (p.output_len == 0) ? xu[0] : B200_LZ;
     const float psi = finish_psi(a, p.w.MB[h] + mx, x0);
-    score_flag(p, a, h, c);
+    score_flag(p, a, h, c, p.w.MB[h]);
     const float sp = p.s_prev ? p.s_prev[h] : 0.f;
     p.log_psi[(int64_t)h * p.V + c] = psi;
     p.scores[(int64_t)h * p.V + c] = psi - sp;
@@ -275,7 +278,7 @@ __global__ void __launch_bounds__(kScore4Threads) prefix_score_full4_kernel(Scor
           psi[q] = p.w.REND[h];
         } else {
           psi[q] = finish_psi(acc[q][j], p.w.MA[h] + mx[q], x0[q]);
-          if ((int64_t)c != last) score_flag(p, acc[q][j], h, c);
+          if ((int64_t)c != last) score_flag(p, acc[q][j], h, c, p.w.MA[h]);
         }
       }
       if (last >= c0 && last < c0 + 4 && last != p.blank && last != p.eos) {
@@ -447,7 +450,7 @@ __global__ void __launch_bounds__(kRingConsumers + 32) prefix_score_ring_kernel(
           psi[q] = p.w.REND[h];
         } else {
           psi[q] = finish_psi(acc[q][j], p.w.MA[h] + mx[q], x0[q]);
-          if ((int64_t)c != last) score_flag(p, acc[q][j], h, c);
+          if ((int64_t)c != last) score_flag(p, acc[q][j], h, c, p.w.MA[h]);
         }
       }
       if (last >= c0 && last < c0 + 4 && last != p.blank && last != p.eos) {
@@ -514,7 +517,7 @@ __global__ void __launch_bounds__(256) prefix_score_partial_kernel(ScoreParams p
   if (lane == 0) {
     const float x0 = (p.output_len == 0) ? xu[0] : B200_LZ;
     const float psi = finish_psi(a, (is_last ? p.w.MB[h] : p.w.MA[h]) + mx, x0);
-    score_flag(p, a, h, c);
+    score_flag(p, a, h, c, is_last ? p.w.MB[h] : p.w.MA[h]);
     const float sp = p.s_prev ? p.s_prev[h] : 0.f;
     p.log_psi[(int64_t)h * p.V + c] = psi;
     p.scores[(int64_t)h * p.V + c] = psi - sp;
@@ -601,7 +604,7 @@ __global__ void __launch_bounds__(kColsThreads) prefix_score_cols_kernel(ScorePa
     const float a = __shfl_sync(0xffffffffu, warp_sum(a0 + a1), 0);  // (one value for the whole warp: the branch below is collective)
     const float x0 = (p.output_len == 0) ? col[0] : B200_LZ;
     float psi;
-    if (a < kScoreAccFloor && n > 0) {
+    if (a < kScoreAccFloor && n > 0 && (is_last ? mb : ma) > 0.5f * B200_LZ) {
       // the scaled sum underflowed: logsumexp over { phi[t-1] + x[t,c] } as written (ctc_prefix_score.py:165-180)
       const float* ph = (is_last ? s_pb : s_pa) - p.start;
       float m = -3.0e38f, sacc = 0.f;

@@ -3,7 +3,7 @@ import cProfile, pstats, sys, torch
 sys.path.insert(0, ".")
 import bench
 dev = torch.device("cuda", 0)
-kw = {"pre_beam": 15} if len(sys.argv) > 1 and sys.argv[1] == "pre" else {}
+kw = {"pre": {"pre_beam": 15}, "window": {"margin": 40}}.get(sys.argv[1] if len(sys.argv) > 1 else "", {})
 bench.bench_decode_loop(dev, **kw)
 pr = cProfile.Profile()
 pr.enable()
