@@ -115,6 +115,7 @@ static int prefix_score_impl(const float* x, const float* x_cols, const float* x
   p.scores = scores; p.log_psi = log_psi;
   p.w = carve_prefix(work, B, T, n_hyps);
   p.xc = x_cols; p.Tc = (int)b200_ctc_prefix_column_stride(T);
+  p.xlens = xlens;
   if (snum > 0 && x_cols) {
     // candidates from the column copy: phi, fill, sums and the exact redo in one kernel, a CTA per hypothesis
     const size_t smem = sizeof(float) * 4 * (size_t)(end > start ? end - start : 0);

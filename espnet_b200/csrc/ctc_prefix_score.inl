@@ -21,6 +21,7 @@ struct ScoreParams {
   int hyp_off;     // the full-vocabulary kernels handle hypotheses [hyp_off, hyp_off + NH) of every utterance
   const float* xc; // (B,V,Tc) column copy of x (b200_ctc_prefix_columns) or null
   int Tc;
+  const int64_t* xlens;  // (B)
 };
 
 // The scaled linear sum loses every term below 2^-126 of the largest representable one (flush to zero).
@@ -40,7 +41,8 @@ __device__ __forceinline__ float finish_psi(float acc, float scale_log, float in
 // prefix has reached -- the exact sum is logzero as well, which is what the scaled sum already returned: nothing to redo.
 // Without this test such a hypothesis queued all V of its tokens: 724 us per position in the windowed search loop.)
 __device__ __forceinline__ void score_flag(const ScoreParams& p, float acc, int h, int c, float m) {
-  if (acc < kScoreAccFloor && p.start < p.end && m > 0.5f * B200_LZ) {
+  // (likewise a window that lies in the utterance's padding: every non-blank log-prob there is logzero)
+  if (acc < kScoreAccFloor && p.start < p.end && m > 0.5f * B200_LZ && p.start < (int)p.xlens[h / p.n_hyps]) {
     const int k = atomicAdd(p.w.fix_count, 1);
     p.w.fix_list[k] = h * p.V + c;
   }
@@ -604,7 +606,7 @@ __global__ void __launch_bounds__(kColsThreads) prefix_score_cols_kernel(ScorePa
     const float a = __shfl_sync(0xffffffffu, warp_sum(a0 + a1), 0);  // (one value for the whole warp: the branch below is collective)
     const float x0 = (p.output_len == 0) ? col[0] : B200_LZ;
     float psi;
-    if (a < kScoreAccFloor && n > 0 && (is_last ? mb : ma) > 0.5f * B200_LZ) {
+    if (a < kScoreAccFloor && n > 0 && (is_last ? mb : ma) > 0.5f * B200_LZ && p.start < (int)xlens[u]) {
       // the scaled sum underflowed: logsumexp over { phi[t-1] + x[t,c] } as written (ctc_prefix_score.py:165-180)
       const float* ph = (is_last ? s_pb : s_pa) - p.start;
       float m = -3.0e38f, sacc = 0.f;

@@ -265,3 +265,40 @@ def test_column_copy_is_the_transpose():
     _lib.check(lib.b200_ctc_prefix_columns(x.data_ptr(), B, T, V, xc.data_ptr(), torch.cuda.current_stream().cuda_stream), "columns")
     assert torch.equal(xc[:, :, :T], x.transpose(1, 2))
     assert torch.isnan(xc[:, :, T:]).all()              # the pad is never written (and never read)
+
+
+@pytest.mark.parametrize("margin", [0, 3])
+def test_hypotheses_without_mass_are_not_queued_for_the_exact_kernel(margin):
+    """A prefix that is longer than its utterance has frames (or whose window holds none of its mass) scores logzero
+    for every token; such hypotheses used to send all V tokens to the exact (log-space) kernel, which returned the same
+    logzero -- 724 us per position late in a windowed search.  On unit-scale inputs hardly anything else underflows:
+    the queue never holds as much as one row."""
+    from espnet_b200.ctc_prefix_score import CTCPrefixScoreB200
+
+    B, T, V, H = 2, 12, 64, 4
+    c = _cases.make_prefix_case(B, T, V, H, seed=77, nsteps=11)
+    if margin:
+        # (a window that STRADDLES the end of a shorter utterance still queues that utterance's tokens for a few
+        # positions -- correct, only slower; the windowed case is run without padding)
+        c["xlens"][:] = T
+    impl = CTCPrefixScoreB200(c["lp"].clone().cuda(), c["xlens"], 0, c["eos"], margin=margin)
+    g = torch.Generator().manual_seed(3)
+    y = torch.full((B * H, 1), c["eos"], dtype=torch.int64, device="cuda")
+    state = None
+    empty_rows = 0
+    for step in range(11):
+        att_w = None
+        if margin:
+            att_w = torch.zeros(B * H, T)
+            att_w[:, min(T - 1, step)] = 1.0
+            att_w = att_w.cuda()
+        scores, st = impl(y, state, None, att_w)
+        queued = int(impl._work.view(torch.int32)[2 * B * T * ((H + 3) & ~3) + 3 * B * H])
+        assert queued < V - 2, (step, queued)   # never a whole row (a few pairs of the padded frames do underflow)
+        empty_rows += int((st[1][:, 1:V - 1] < -1e9).all(1).sum())
+        hyp = torch.randint(0, H, (B, H), generator=g)
+        tok = torch.full((B, H), 5)                         # "5 5 5 ...": L labels need 2L - 1 frames
+        state = impl.index_select_state(st, (hyp * V + tok).cuda())
+        parent = (hyp + torch.arange(B).view(-1, 1) * H).view(-1).cuda()
+        y = torch.cat([y[parent], tok.view(-1, 1).cuda()], dim=1)
+    assert empty_rows > 0   # the walk did reach hypotheses without mass
