@@ -89,6 +89,13 @@ __global__ void __cluster_dims__(kPruneCtas, 1, 1) __launch_bounds__(kPruneThrea
   const int per_warp = (((c1 - c0 + kWarps - 1) / kWarps) + 31) & ~31;
   const int w0 = min(c0 + warp * per_warp, c1), w1 = min(w0 + per_warp, c1);
   auto walk = [&](auto&& visit) {  // visit(valid, j, value): called by all 32 lanes together, j ascending
+    // (hypothesis, token) of the lane's element: one division per warp range, increments after that
+    int hh = 0, cc = 0;
+    if (w0 < w1) {
+      const int j0 = min(w0 + lane, w1 - 1);
+      hh = j0 / p.V;
+      cc = j0 - hh * p.V;
+    }
     for (int base = w0; base < w1; base += 128) {
       float a[4], c4[4], vs[4];
       int jj[4];
@@ -98,8 +105,12 @@ __global__ void __cluster_dims__(kPruneCtas, 1, 1) __launch_bounds__(kPruneThrea
         const int j = base + 32 * x + lane;
         jj[x] = j;
         ok[x] = j < w1;
-        const int jc = ok[x] ? j : w0;
-        const int h = jc / p.V, c = jc - h * p.V;
+        // (hh, cc) belong to min(j, the last valid element this lane reached): an invalid lane re-reads a valid address
+        const int h = hh, c = cc;
+        if (j + 32 < w1) {
+          cc += 32;
+          while (cc >= p.V) { cc -= p.V; ++hh; }
+        }
         const int64_t o = (int64_t)(u * p.beam + h) * p.V + c;
         a[x] = p.att[o];
         c4[x] = p.ctc ? p.ctc[o] : 0.f;
